@@ -1,0 +1,164 @@
+/*
+ * heat.h -- C ABI of libheat_b200.so, the B200 (sm_100a) replacement for the
+ * SOLVER LOOP of manospits/parallel_heat.
+ *
+ * The reference has no library interface: its solver loop is inline in main()
+ *     M = mpi/mpi_heat_improved_persistent_stat.c   (loop M:129-269)
+ *     C = cuda/cuda_heat.cu                         (loop C:176-242)
+ * so every entry point below cites the region of those files it stands for.
+ * Plain C, plain pointers and sizes; no CUDA or torch types in any signature
+ * (streams and device pointers travel as void*).  Every function returns
+ * HEAT_OK (0) or a negative HEAT_E_* code and never calls exit();
+ * heat_last_error() gives the text for the calling thread.
+ *
+ * Grid layout is the reference's: dense row-major u[ix*ny + iy], iy fastest,
+ * nx rows (M:320, C:279).  The ring (row 0, row nx-1, col 0, col ny-1) is never
+ * updated (guards M:187, C:57).
+ */
+#ifndef HEAT_B200_H
+#define HEAT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HEAT_OK            0
+#define HEAT_E_INVALID    -1 /* bad argument                                      */
+#define HEAT_E_CUDA       -2 /* a CUDA runtime call failed (see heat_last_error)  */
+#define HEAT_E_NOMEM      -3 /* host or device allocation failed                  */
+#define HEAT_E_STATE      -4 /* call not valid in the handle's current state      */
+#define HEAT_E_PEER       -5 /* neighbour strip missing / peer access unavailable */
+#define HEAT_E_TIMEOUT    -6 /* a neighbour strip did not arrive in time          */
+
+/* Arithmetic of one update, selecting which reference build is reproduced bit for bit. */
+#define HEAT_F32_FMA     0 /* C:155-161 as nvcc builds it by default: float, 2 FFMA       */
+#define HEAT_F32_NOFMA   1 /* C:155-161 with -fmad=false: float, every op rounded         */
+#define HEAT_MPI_F64MIX  2 /* M:168-174: float neighbour sums, rest in double (2.0 literal) */
+
+/* How many updates `steps` means, and when convergence is checked. */
+#define HEAT_STEPS_CUDA  0 /* `steps` updates                 (C:204  i <  STEPS) */
+#define HEAT_STEPS_MPI   1 /* `steps`+1 updates               (M:159  it <= STEPS) */
+#define HEAT_PHASE_MPI   0 /* check after update it when (it+1)%K==0 (M:157,236-238) */
+#define HEAT_PHASE_CUDA  1 /* check after update it when  it   %K==0 (C:219)         */
+
+/* Run-time form of the reference's compile-time parameters
+ * (NXPROB, NYPROB, STEPS, STEP, CONVERGE: M:7-21, C:7-23; struct Parms M:29-32). */
+typedef struct heat_params {
+    int   nx, ny;          /* NXPROB, NYPROB: rows, row length                         */
+    int   steps;           /* STEPS                                                    */
+    float cx, cy;          /* parms.cx (row +-1 term), parms.cy (col +-1 term); 0.1f    */
+    int   conv_every;      /* STEP / CHECK_INTERVAL; 0 = built without -DCONVERGE      */
+    float conv_eps;        /* converged <=> every |old-new| < conv_eps; 1e-3f (M:245,C:67) */
+    int   conv_phase;      /* HEAT_PHASE_*                                             */
+    int   step_convention; /* HEAT_STEPS_*                                             */
+    int   arith;           /* HEAT_F32_FMA | HEAT_F32_NOFMA | HEAT_MPI_F64MIX          */
+    int   temporal_block;  /* updates fused per pass over HBM: 1, 2 or 4               */
+    int   device;          /* CUDA device ordinal of this strip                        */
+    int   rank, nranks;    /* row-strip decomposition: this handle owns strip `rank`   */
+} heat_params;
+
+typedef struct heat_handle heat_handle; /* opaque: owns device buffers, stream, graphs */
+
+/* Fills *p with the reference's defaults: 20x20, steps 100, cx=cy=0.1, no convergence
+ * check, conv_eps 1e-3, F32_FMA, CUDA conventions, 1 strip on device 0 (M:7-32, C:7-23). */
+int heat_params_default(heat_params *p);
+
+const char *heat_last_error(void);
+/* 1 if a CUDA device is usable by this process, else 0 (never fails). */
+int heat_device_count(void);
+
+/* ---- the reference's helpers, same arguments (M:315-341, C:274-300) ------------------ */
+/* inidat: u[ix*ny+iy] = (float)(ix*(nx-ix-1)*iy*(ny-iy-1)) in wrapping int32 (M:320). */
+int heat_inidat(int nx, int ny, float *u);
+/* prtdat: "%6.1f" text, iy descending outer, ix ascending inner (M:326-341). */
+int heat_prtdat(int nx, int ny, const float *u, const char *fnam);
+/* Binary twin of prtdat: 16-byte header {"HEATB200", int32 nx, int32 ny} + nx*ny floats. */
+int heat_prtdat_bin(int nx, int ny, const float *u, const char *fnam);
+int heat_readdat_bin(const char *fnam, int *nx, int *ny, float *u, size_t capacity_floats);
+
+/* ---- one-shot: the whole loop region with caller-owned HOST memory -------------------
+ * Replaces C:176-242 (cudaMalloc, H2D to both buffers, step loop, D2H) and, on one strip,
+ * M:129-269.  grid: in = initial field, out = newest field.  updates_done = Jacobi updates
+ * executed; the reference programs print updates_done-1 when they converge (M:302, C:256). */
+int heat_solve(const heat_params *p, float *grid, int *updates_done, int *converged);
+
+/* ---- device-resident handle (what C keeps alive in dvc_grids[2], C:177-198) ---------- */
+int heat_create(const heat_params *p, heat_handle **out);
+int heat_destroy(heat_handle *h);
+/* Use the caller's CUDA stream (a cudaStream_t passed as void*) instead of the handle's own. */
+int heat_set_stream(heat_handle *h, void *cuda_stream);
+/* Host -> device of the FULL nx*ny field into BOTH buffers (C:197-198); a strip takes its rows. */
+int heat_upload(heat_handle *h, const float *full_grid);
+/* Same from a device pointer holding the full field (used when the field is already in HBM). */
+int heat_upload_device(heat_handle *h, const void *d_full_grid);
+/* inidat evaluated on the device straight into both buffers (bit-identical to heat_inidat). */
+int heat_init_inidat(heat_handle *h);
+/* Runs the time loop: `steps` interpreted per params.step_convention; stops early when the
+ * convergence check (params.conv_every) succeeds.  Asynchronous work is complete on return.
+ * Replaces C:204-238 / M:159-265.  May be called repeatedly; the update counter that drives
+ * conv_phase continues across calls. */
+int heat_run(heat_handle *h, int steps, int *updates_done, int *converged);
+/* Enqueue `updates` plain updates (no convergence check) on the stream and return without
+ * waiting: the timed region of a benchmark. */
+int heat_enqueue(heat_handle *h, int updates);
+/* Wait for everything enqueued on the handle's stream; HEAT_E_TIMEOUT if a neighbour strip
+ * never arrived. */
+int heat_sync(heat_handle *h);
+/* Device time of the last heat_run's loop (CUDA events around the loop only). */
+int heat_elapsed_ms(heat_handle *h, float *ms);
+/* max |old-new| over this strip for the most recent update (runs one reduction pass). */
+int heat_residual(heat_handle *h, float *residual);
+/* Newest field -> host; a strip writes only the rows it owns into full_grid. */
+int heat_download(heat_handle *h, float *full_grid);
+/* Device pointer / pitch (in floats) / local row count of the newest (which=0) or older
+ * (which=1) buffer, and the global row of local row 0. */
+int heat_device_view(heat_handle *h, int which, void **d_ptr, int64_t *pitch, int *local_rows, int *first_global_row);
+/* Kernels launched by this handle so far (benchmarks report it). */
+int heat_launch_count(heat_handle *h, int64_t *launches);
+
+/* ---- stateless single update on caller-owned DEVICE memory ---------------------------
+ * One Jacobi update of the interior of a dense nx*ny field (pitch = ny): the body of the
+ * reference kernels C:140-163 (plain) and C:42-138 (with the convergence reduction fused;
+ * d_residual_bits receives max|old-new| as float bits via atomicMax and must be zeroed by
+ * the caller).  d_out's ring is left untouched.  stream: cudaStream_t as void*, may be NULL. */
+int heat_step_device(const void *d_in, void *d_out, int nx, int ny, float cx, float cy, int arith, void *stream);
+int heat_step_residual_device(const void *d_in, void *d_out, int nx, int ny, float cx, float cy, int arith,
+                              void *d_residual_bits, void *stream);
+
+/* ---- row strips across GPUs (replaces the 2-D block topology + persistent halo requests,
+ *      M:51-84,130-155,160-161,177,263) --------------------------------------------------
+ * Strip r of n owns global rows [row0, row0+rows).  Each strip keeps one ghost row per
+ * neighbour; after every update a strip stores its first/last owned row straight into the
+ * neighbour's ghost row over NVLink and then raises the neighbour's step flag. */
+int heat_strip_rows(int nx, int nranks, int rank, int *row0, int *rows);
+/* Who moves the ghost rows: HEAT_HALO_P2P (default) = the update kernel stores them into the
+ * connected neighbours; HEAT_HALO_EXTERNAL = the caller copies row 1 / row n-2 of the newest
+ * buffer into the neighbours' ghost rows between updates (e.g. NCCL send/recv on the
+ * handle's stream), and no connection is needed. */
+#define HEAT_HALO_P2P      0
+#define HEAT_HALO_EXTERNAL 1
+int heat_set_halo_mode(heat_handle *h, int mode);
+#define HEAT_IPC_BLOB_BYTES 256
+/* Export this strip's buffers + flags for another PROCESS (CUDA IPC handles). */
+int heat_ipc_export(heat_handle *h, void *blob, size_t blob_bytes);
+/* Connect neighbours from blobs (NULL = no neighbour on that side == MPI_PROC_NULL, M:68). */
+int heat_ipc_connect(heat_handle *h, const void *north_blob, const void *south_blob);
+/* Connect neighbours living in THIS process (one host thread driving several GPUs, or several
+ * strips on one GPU).  Such strips are ordered with CUDA events and must be driven together,
+ * update by update, through heat_group_run / heat_group_enqueue; upload every strip first. */
+int heat_connect_local(heat_handle *h, heat_handle *north, heat_handle *south);
+int heat_group_run(heat_handle **strips, int n, int steps, int *updates_done, int *converged);
+int heat_group_enqueue(heat_handle **strips, int n, int updates);
+/* Convergence across strips in OTHER processes: every conv_every updates heat_run hands the
+ * local max|old-new| to this callback, which must return the maximum over all strips in
+ * *value (one 4-byte max-allreduce; replaces MPI_Allreduce(LAND), M:255).  Return 0 on success. */
+typedef int (*heat_allreduce_max_fn)(float *value, void *ctx);
+int heat_set_allreduce_max(heat_handle *h, heat_allreduce_max_fn fn, void *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HEAT_B200_H */

@@ -1,0 +1,796 @@
+// heat_api.cu -- the C ABI declared in include/heat.h: handle, buffers, stream, time loop.
+// Host code only drives the device; there is NO CPU computation path: without a usable
+// CUDA device every compute entry point fails with HEAT_E_CUDA.
+#include "../../include/heat.h"
+#include "heat_kernels.cuh"
+
+#include <cuda.h>
+#include <new>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+using namespace heatk;
+
+// ------------------------------------------------------------------ errors
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CK(call)                                                                                        \
+    do {                                                                                                \
+        cudaError_t e_ = (call);                                                                        \
+        if (e_ != cudaSuccess)                                                                          \
+            return fail(HEAT_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+extern "C" const char* heat_last_error(void) { return g_err; }
+
+extern "C" int heat_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+extern "C" int heat_params_default(heat_params* p)
+{
+    if (!p) return fail(HEAT_E_INVALID, "heat_params_default: null");
+    memset(p, 0, sizeof *p);
+    p->nx = p->ny = 20; // NXPROB/NYPROB defaults (M:7-12, C:7-12)
+    p->steps = 100;     // M:16-18
+    p->cx = p->cy = 0.1f;
+    p->conv_every = 0;
+    p->conv_eps = 1e-3f;
+    p->conv_phase = HEAT_PHASE_CUDA;
+    p->step_convention = HEAT_STEPS_CUDA;
+    p->arith = HEAT_F32_FMA;
+    p->temporal_block = 1;
+    p->device = 0;
+    p->rank = 0;
+    p->nranks = 1;
+    return HEAT_OK;
+}
+
+// ------------------------------------------------------------------ host helpers (M:315-341)
+extern "C" int heat_inidat(int nx, int ny, float* u)
+{
+    if (nx < 1 || ny < 1 || !u) return fail(HEAT_E_INVALID, "heat_inidat: bad arguments");
+    for (int ix = 0; ix < nx; ix++) {
+        const uint32_t a = (uint32_t)ix * (uint32_t)(nx - ix - 1);
+        float* row = u + (size_t)ix * ny;
+        for (int iy = 0; iy < ny; iy++) row[iy] = (float)(int32_t)(a * (uint32_t)iy * (uint32_t)(ny - iy - 1));
+    }
+    return HEAT_OK;
+}
+
+extern "C" int heat_prtdat(int nx, int ny, const float* u, const char* fnam)
+{
+    if (nx < 1 || ny < 1 || !u || !fnam) return fail(HEAT_E_INVALID, "heat_prtdat: bad arguments");
+    FILE* fp = fopen(fnam, "w");
+    if (!fp) return fail(HEAT_E_INVALID, "heat_prtdat: cannot open %s", fnam);
+    // one text row per iy (descending), nx values each
+    for (int iy = ny - 1; iy >= 0; iy--) {
+        for (int ix = 0; ix < nx; ix++) {
+            fprintf(fp, "%6.1f", u[(size_t)ix * ny + iy]);
+            fputc(ix == nx - 1 ? '\n' : ' ', fp);
+        }
+    }
+    if (fclose(fp)) return fail(HEAT_E_INVALID, "heat_prtdat: write to %s failed", fnam);
+    return HEAT_OK;
+}
+
+struct bin_header {
+    char magic[8];
+    int32_t nx, ny;
+};
+
+extern "C" int heat_prtdat_bin(int nx, int ny, const float* u, const char* fnam)
+{
+    if (nx < 1 || ny < 1 || !u || !fnam) return fail(HEAT_E_INVALID, "heat_prtdat_bin: bad arguments");
+    FILE* fp = fopen(fnam, "wb");
+    if (!fp) return fail(HEAT_E_INVALID, "heat_prtdat_bin: cannot open %s", fnam);
+    bin_header h;
+    memcpy(h.magic, "HEATB200", 8);
+    h.nx = nx;
+    h.ny = ny;
+    const size_t n = (size_t)nx * ny;
+    int ok = fwrite(&h, sizeof h, 1, fp) == 1 && fwrite(u, sizeof(float), n, fp) == n;
+    ok = (fclose(fp) == 0) && ok;
+    return ok ? HEAT_OK : fail(HEAT_E_INVALID, "heat_prtdat_bin: write to %s failed", fnam);
+}
+
+extern "C" int heat_readdat_bin(const char* fnam, int* nx, int* ny, float* u, size_t capacity_floats)
+{
+    if (!fnam || !nx || !ny) return fail(HEAT_E_INVALID, "heat_readdat_bin: bad arguments");
+    FILE* fp = fopen(fnam, "rb");
+    if (!fp) return fail(HEAT_E_INVALID, "heat_readdat_bin: cannot open %s", fnam);
+    bin_header h;
+    if (fread(&h, sizeof h, 1, fp) != 1 || memcmp(h.magic, "HEATB200", 8) != 0 || h.nx < 1 || h.ny < 1) {
+        fclose(fp);
+        return fail(HEAT_E_INVALID, "heat_readdat_bin: %s is not a HEATB200 dump", fnam);
+    }
+    *nx = h.nx;
+    *ny = h.ny;
+    int rc = HEAT_OK;
+    if (u) {
+        const size_t n = (size_t)h.nx * h.ny;
+        if (n > capacity_floats)
+            rc = fail(HEAT_E_INVALID, "heat_readdat_bin: buffer too small (%zu < %zu)", capacity_floats, n);
+        else if (fread(u, sizeof(float), n, fp) != n)
+            rc = fail(HEAT_E_INVALID, "heat_readdat_bin: %s is truncated", fnam);
+    }
+    fclose(fp);
+    return rc;
+}
+
+// ------------------------------------------------------------------ strips
+extern "C" int heat_strip_rows(int nx, int nranks, int rank, int* row0, int* rows)
+{
+    if (nx < 1 || nranks < 1 || rank < 0 || rank >= nranks || nranks > nx)
+        return fail(HEAT_E_INVALID, "heat_strip_rows: nx=%d nranks=%d rank=%d", nx, nranks, rank);
+    // balanced split; the reference assumes divisibility (M:72-73), this does not
+    const int base = nx / nranks, rem = nx % nranks;
+    const int r0 = rank * base + (rank < rem ? rank : rem);
+    if (row0) *row0 = r0;
+    if (rows) *rows = base + (rank < rem ? 1 : 0);
+    return HEAT_OK;
+}
+
+// ------------------------------------------------------------------ handle
+struct peer_side {
+    float* buf[2] = {nullptr, nullptr};   // neighbour's two buffers (peer-mapped)
+    unsigned long long* flag = nullptr;   // neighbour's flag slot that this strip writes
+    int nloc = 0;
+    void* ipc_base[3] = {nullptr, nullptr, nullptr}; // bases opened with cudaIpcOpenMemHandle
+};
+
+struct heat_handle {
+    heat_params p;
+    int row0 = 0, rows_own = 0; // owned global rows [row0, row0+rows_own)
+    int lo = 0, nloc = 0;       // local array = global rows [lo, lo+nloc)
+    int64_t pitch = 0;          // floats
+    float* buf[2] = {nullptr, nullptr};
+    int cur = 0;                // index of the newest buffer
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    unsigned* d_resid = nullptr;
+    unsigned* h_resid = nullptr; // pinned
+    int* d_status = nullptr;     // mapped pinned: wait-kernel time-outs
+    int* h_status = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_resid = nullptr;
+    float last_ms = 0.0f;
+    long long it = 0;            // updates since the last upload (drives conv_phase)
+    unsigned long long seq = 0;  // monotonic epoch for the strip flags
+    int64_t launches = 0;
+    int rows_per_tile = 0;
+    int sm_count = 148;
+    // neighbours: side 0 = north (lower rows), 1 = south
+    unsigned long long* flags = nullptr; // [0] written by north neighbour, [1] by south
+    peer_side peer[2];
+    bool connected = false;
+    // neighbours in this process are ordered with events instead of flags (no spinning kernels)
+    heat_handle* local_nb[2] = {nullptr, nullptr};
+    cudaEvent_t ev_done[2] = {nullptr, nullptr}; // recorded after epoch e in ev_done[e & 1]
+    bool serpentine = true;
+    bool external_halo = false; // the caller moves the ghost rows between updates
+    heat_allreduce_max_fn allreduce = nullptr; // joins the residuals of strips in other processes
+    void* allreduce_ctx = nullptr;
+};
+
+struct ipc_blob {
+    char magic[8];
+    cudaIpcMemHandle_t mem[3]; // buf0, buf1, flags
+    int64_t offset[3];         // of the pointer inside the exported allocation
+    int32_t nloc, rank, nranks, pad;
+    int64_t pitch;
+};
+static_assert(sizeof(ipc_blob) <= HEAT_IPC_BLOB_BYTES, "ipc blob too large");
+
+static int env_int(const char* k, int dflt)
+{
+    const char* v = getenv(k);
+    return (v && *v) ? atoi(v) : dflt;
+}
+
+static int validate(const heat_params* p)
+{
+    if (!p) return fail(HEAT_E_INVALID, "params: null");
+    if (p->nx < 1 || p->ny < 1) return fail(HEAT_E_INVALID, "params: nx=%d ny=%d", p->nx, p->ny);
+    if (p->steps < 0) return fail(HEAT_E_INVALID, "params: steps=%d", p->steps);
+    if (p->conv_every < 0) return fail(HEAT_E_INVALID, "params: conv_every=%d", p->conv_every);
+    if (p->arith < HEAT_F32_FMA || p->arith > HEAT_MPI_F64MIX) return fail(HEAT_E_INVALID, "params: arith=%d", p->arith);
+    if (p->temporal_block != 1 && p->temporal_block != 2 && p->temporal_block != 4)
+        return fail(HEAT_E_INVALID, "params: temporal_block=%d (1, 2 or 4)", p->temporal_block);
+    if (p->nranks < 1 || p->rank < 0 || p->rank >= p->nranks)
+        return fail(HEAT_E_INVALID, "params: rank=%d nranks=%d", p->rank, p->nranks);
+    if (p->nranks > 1 && p->nx / p->nranks < 2)
+        return fail(HEAT_E_INVALID, "params: %d rows cannot be cut into %d strips of >= 2 rows", p->nx, p->nranks);
+    if (p->conv_phase != HEAT_PHASE_MPI && p->conv_phase != HEAT_PHASE_CUDA)
+        return fail(HEAT_E_INVALID, "params: conv_phase=%d", p->conv_phase);
+    if (p->step_convention != HEAT_STEPS_CUDA && p->step_convention != HEAT_STEPS_MPI)
+        return fail(HEAT_E_INVALID, "params: step_convention=%d", p->step_convention);
+    return HEAT_OK;
+}
+
+extern "C" int heat_destroy(heat_handle* h)
+{
+    if (!h) return HEAT_OK;
+    cudaSetDevice(h->p.device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    for (int s = 0; s < 2; s++)
+        for (int k = 0; k < 3; k++)
+            if (h->peer[s].ipc_base[k]) cudaIpcCloseMemHandle(h->peer[s].ipc_base[k]);
+    if (h->buf[0]) cudaFree(h->buf[0]);
+    if (h->buf[1]) cudaFree(h->buf[1]);
+    if (h->flags) cudaFree(h->flags);
+    if (h->d_resid) cudaFree(h->d_resid);
+    if (h->h_resid) cudaFreeHost(h->h_resid);
+    if (h->h_status) cudaFreeHost(h->h_status);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->ev_resid) cudaEventDestroy(h->ev_resid);
+    for (int k = 0; k < 2; k++)
+        if (h->ev_done[k]) cudaEventDestroy(h->ev_done[k]);
+    if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
+    cudaGetLastError();
+    delete h;
+    return HEAT_OK;
+}
+
+extern "C" int heat_create(const heat_params* p, heat_handle** out)
+{
+    if (!out) return fail(HEAT_E_INVALID, "heat_create: null out");
+    *out = nullptr;
+    int rc = validate(p);
+    if (rc) return rc;
+    int ndev = 0;
+    CK(cudaGetDeviceCount(&ndev));
+    if (p->device < 0 || p->device >= ndev) return fail(HEAT_E_INVALID, "heat_create: device %d of %d", p->device, ndev);
+    CK(cudaSetDevice(p->device));
+
+    heat_handle* h = new (std::nothrow) heat_handle();
+    if (!h) return fail(HEAT_E_NOMEM, "heat_create: out of host memory");
+    h->p = *p;
+    heat_strip_rows(p->nx, p->nranks, p->rank, &h->row0, &h->rows_own);
+    // local array: owned rows plus one ghost row towards each existing neighbour
+    h->lo = (p->rank > 0) ? h->row0 - 1 : 0;
+    const int hi = (p->rank < p->nranks - 1) ? h->row0 + h->rows_own + 1 : p->nx;
+    h->nloc = hi - h->lo;
+    // rows padded to 128 bytes so that every row starts on a float4 (and a cache line)
+    h->pitch = ((int64_t)p->ny + 31) / 32 * 32;
+
+    const size_t bytes = (size_t)h->nloc * h->pitch * sizeof(float);
+#define CKH(call)                                                                                      \
+    do {                                                                                               \
+        cudaError_t e_ = (call);                                                                       \
+        if (e_ != cudaSuccess) {                                                                       \
+            int c_ = (e_ == cudaErrorMemoryAllocation) ? HEAT_E_NOMEM : HEAT_E_CUDA;                   \
+            fail(c_, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__);      \
+            heat_destroy(h);                                                                           \
+            return c_;                                                                                 \
+        }                                                                                              \
+    } while (0)
+    CKH(cudaMalloc((void**)&h->buf[0], bytes));
+    CKH(cudaMalloc((void**)&h->buf[1], bytes));
+    CKH(cudaMalloc((void**)&h->flags, 2 * sizeof(unsigned long long)));
+    CKH(cudaMalloc((void**)&h->d_resid, sizeof(unsigned)));
+    CKH(cudaHostAlloc((void**)&h->h_resid, sizeof(unsigned), cudaHostAllocDefault));
+    CKH(cudaHostAlloc((void**)&h->h_status, sizeof(int), cudaHostAllocMapped));
+    *h->h_status = 0;
+    CKH(cudaHostGetDevicePointer((void**)&h->d_status, h->h_status, 0));
+    CKH(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    h->own_stream = true;
+    CKH(cudaMemsetAsync(h->buf[0], 0, bytes, h->stream));
+    CKH(cudaMemsetAsync(h->buf[1], 0, bytes, h->stream));
+    CKH(cudaMemsetAsync(h->flags, 0, 2 * sizeof(unsigned long long), h->stream));
+    CKH(cudaMemsetAsync(h->d_resid, 0, sizeof(unsigned), h->stream));
+    CKH(cudaEventCreate(&h->ev0));
+    CKH(cudaEventCreate(&h->ev1));
+    CKH(cudaEventCreateWithFlags(&h->ev_resid, cudaEventDisableTiming));
+    CKH(cudaEventCreateWithFlags(&h->ev_done[0], cudaEventDisableTiming));
+    CKH(cudaEventCreateWithFlags(&h->ev_done[1], cudaEventDisableTiming));
+    CKH(cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, p->device));
+    CKH(cudaStreamSynchronize(h->stream));
+#undef CKH
+    h->rows_per_tile = env_int("HEAT_ROWS_PER_TILE", 0);
+    h->serpentine = env_int("HEAT_SERPENTINE", 1) != 0;
+    *out = h;
+    return HEAT_OK;
+}
+
+extern "C" int heat_set_stream(heat_handle* h, void* cuda_stream)
+{
+    if (!h) return fail(HEAT_E_INVALID, "heat_set_stream: null handle");
+    CK(cudaSetDevice(h->p.device));
+    CK(cudaStreamSynchronize(h->stream));
+    if (h->own_stream) {
+        cudaStreamDestroy(h->stream);
+        h->own_stream = false;
+    }
+    h->stream = (cudaStream_t)cuda_stream;
+    return HEAT_OK;
+}
+
+// ------------------------------------------------------------------ launches
+static int pick_rows_per_tile(const heat_handle* h, int threads)
+{
+    if (h->rows_per_tile > 0) return h->rows_per_tile;
+    // enough row tiles that the grid is several waves of 148 SMs, but tiles tall enough
+    // that the two halo rows re-read per tile stay a small fraction
+    const int interior = h->nloc - 2;
+    const int64_t col_blocks = (h->pitch / 4 + threads - 1) / threads;
+    int r = 32;
+    while (r > 4 && col_blocks * ((interior + r - 1) / r) < (int64_t)h->sm_count * 16) r >>= 1;
+    return r;
+}
+
+template <int ARITH, bool RESID>
+static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, float* peer_n, float* peer_s, int reverse)
+{
+    const int nloc = h->nloc, ny = h->p.ny;
+    if (nloc < 3 || ny < 3) return cudaSuccess; // no interior: nothing to update (ring only)
+    constexpr int THREADS = 128, UNROLL = 4;
+    const int rpt = pick_rows_per_tile(h, THREADS);
+    dim3 grid((unsigned)((h->pitch / 4 + THREADS - 1) / THREADS), (unsigned)((nloc - 2 + rpt - 1) / rpt));
+    if (grid.y > 65535u) { // fall back to taller tiles
+        const int rpt2 = (nloc - 2 + 65534) / 65535;
+        grid.y = (unsigned)((nloc - 2 + rpt2 - 1) / rpt2);
+        heat_step_vec<ARITH, RESID, THREADS, UNROLL><<<grid, THREADS, 0, h->stream>>>(
+            in, out, nloc, ny, h->pitch, rpt2, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, reverse);
+    } else {
+        heat_step_vec<ARITH, RESID, THREADS, UNROLL><<<grid, THREADS, 0, h->stream>>>(
+            in, out, nloc, ny, h->pitch, rpt, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, reverse);
+    }
+    h->launches++;
+    return cudaGetLastError();
+}
+
+static cudaError_t launch_step(heat_handle* h, bool resid, const float* in, float* out, float* peer_n, float* peer_s,
+                               int reverse)
+{
+    switch (h->p.arith * 2 + (resid ? 1 : 0)) {
+    case 0: return launch_step_t<HEAT_ARITH_F32_FMA, false>(h, in, out, peer_n, peer_s, reverse);
+    case 1: return launch_step_t<HEAT_ARITH_F32_FMA, true>(h, in, out, peer_n, peer_s, reverse);
+    case 2: return launch_step_t<HEAT_ARITH_F32_NOFMA, false>(h, in, out, peer_n, peer_s, reverse);
+    case 3: return launch_step_t<HEAT_ARITH_F32_NOFMA, true>(h, in, out, peer_n, peer_s, reverse);
+    case 4: return launch_step_t<HEAT_ARITH_F64MIX, false>(h, in, out, peer_n, peer_s, reverse);
+    default: return launch_step_t<HEAT_ARITH_F64MIX, true>(h, in, out, peer_n, peer_s, reverse);
+    }
+}
+
+static const unsigned long long WAIT_TIMEOUT_NS = 20ull * 1000000000ull;
+
+// one update: [wait for neighbours] -> step kernel (also stores the ghost rows of the
+// neighbours) -> [signal neighbours] -> swap
+static int enqueue_update(heat_handle* h, bool resid)
+{
+    const bool has_n = !h->external_halo && h->p.rank > 0, has_s = !h->external_halo && h->p.rank < h->p.nranks - 1;
+    const bool strips = has_n || has_s;
+    if (strips && !h->connected)
+        return fail(HEAT_E_PEER, "strip %d of %d is not connected to its neighbours", h->p.rank, h->p.nranks);
+    const bool local = h->local_nb[0] || h->local_nb[1];
+    const float* in = h->buf[h->cur];
+    float* out = h->buf[1 - h->cur];
+    float *pn = nullptr, *ps = nullptr;
+    if (strips) {
+        if (local) {
+            // neighbour's epoch `seq` (its previous update, or its upload) must be complete
+            for (int side = 0; side < 2; side++)
+                if (h->local_nb[side]) CK(cudaStreamWaitEvent(h->stream, h->local_nb[side]->ev_done[h->seq & 1], 0));
+        } else {
+            heat_wait<<<1, 32, 0, h->stream>>>(has_n ? &h->flags[0] : nullptr, has_s ? &h->flags[1] : nullptr, h->seq,
+                                               WAIT_TIMEOUT_NS, h->d_status);
+            h->launches++;
+        }
+        // my first owned row (local row 1) is the north neighbour's bottom ghost row, and vice versa
+        if (has_n) pn = h->peer[0].buf[1 - h->cur] + (int64_t)(h->peer[0].nloc - 1) * h->pitch;
+        if (has_s) ps = h->peer[1].buf[1 - h->cur];
+    }
+    if (resid) CK(cudaMemsetAsync(h->d_resid, 0, sizeof(unsigned), h->stream));
+    const int reverse = h->serpentine ? (int)(h->it & 1) : 0;
+    CK(launch_step(h, resid, in, out, pn, ps, reverse));
+    h->seq++;
+    if (strips) {
+        if (local) {
+            CK(cudaEventRecord(h->ev_done[h->seq & 1], h->stream));
+        } else {
+            heat_signal<<<1, 32, 0, h->stream>>>(has_n ? h->peer[0].flag : nullptr, has_s ? h->peer[1].flag : nullptr, h->seq);
+            h->launches++;
+        }
+    }
+    CK(cudaGetLastError());
+    h->cur = 1 - h->cur;
+    h->it++;
+    return HEAT_OK;
+}
+
+extern "C" int heat_group_enqueue(heat_handle** hs, int n, int updates)
+{
+    if (!hs || n < 1 || updates < 0) return fail(HEAT_E_INVALID, "heat_group_enqueue: bad arguments");
+    // update by update across the strips: the event ordering between local strips relies on it
+    for (int i = 0; i < updates; i++)
+        for (int k = 0; k < n; k++) {
+            CK(cudaSetDevice(hs[k]->p.device));
+            int rc = enqueue_update(hs[k], false);
+            if (rc) return rc;
+        }
+    return HEAT_OK;
+}
+
+extern "C" int heat_enqueue(heat_handle* h, int updates)
+{
+    if (!h) return fail(HEAT_E_INVALID, "heat_enqueue: null handle");
+    if (h->local_nb[0] || h->local_nb[1]) return fail(HEAT_E_STATE, "heat_enqueue: locally connected strips run through heat_group_*");
+    return heat_group_enqueue(&h, 1, updates);
+}
+
+extern "C" int heat_sync(heat_handle* h)
+{
+    if (!h) return fail(HEAT_E_INVALID, "heat_sync: null handle");
+    CK(cudaSetDevice(h->p.device));
+    CK(cudaStreamSynchronize(h->stream));
+    if (*h->h_status) return fail(HEAT_E_TIMEOUT, "strip %d: neighbour did not arrive within 20 s", h->p.rank);
+    return HEAT_OK;
+}
+
+extern "C" int heat_set_allreduce_max(heat_handle* h, heat_allreduce_max_fn fn, void* ctx)
+{
+    if (!h) return fail(HEAT_E_INVALID, "heat_set_allreduce_max: null handle");
+    h->allreduce = fn;
+    h->allreduce_ctx = ctx;
+    return HEAT_OK;
+}
+
+// The time loop (C:204-238 / M:159-265) over one strip or over all strips of this process.
+extern "C" int heat_group_run(heat_handle** hs, int n, int steps, int* updates_done, int* converged)
+{
+    if (!hs || n < 1 || steps < 0) return fail(HEAT_E_INVALID, "heat_run: bad arguments");
+    for (int k = 0; k < n; k++)
+        if (!hs[k]) return fail(HEAT_E_INVALID, "heat_run: null handle");
+    heat_handle* h0 = hs[0];
+    const long long total = (long long)steps + (h0->p.step_convention == HEAT_STEPS_MPI ? 1 : 0);
+    const int K = h0->p.conv_every;
+    long long done = 0;
+    int conv = 0;
+    for (int k = 0; k < n; k++) {
+        CK(cudaSetDevice(hs[k]->p.device));
+        CK(cudaEventRecord(hs[k]->ev0, hs[k]->stream));
+    }
+    while (done < total && !conv) {
+        // is update number `it` one whose result is checked?
+        const bool check = K > 0 && (h0->p.conv_phase == HEAT_PHASE_CUDA ? (h0->it % K == 0) : ((h0->it + 1) % K == 0));
+        for (int k = 0; k < n; k++) {
+            CK(cudaSetDevice(hs[k]->p.device));
+            int rc = enqueue_update(hs[k], check);
+            if (rc) return rc;
+            if (check) {
+                // one 4-byte read-back per K updates: the only host sync in the loop
+                CK(cudaMemcpyAsync(hs[k]->h_resid, hs[k]->d_resid, sizeof(unsigned), cudaMemcpyDeviceToHost, hs[k]->stream));
+                CK(cudaEventRecord(hs[k]->ev_resid, hs[k]->stream));
+            }
+        }
+        done++;
+        if (check) {
+            float r = 0.0f;
+            for (int k = 0; k < n; k++) {
+                CK(cudaEventSynchronize(hs[k]->ev_resid));
+                float rk;
+                memcpy(&rk, hs[k]->h_resid, sizeof rk);
+                r = fmaxf(r, rk);
+            }
+            // strips in other processes: one small max-allreduce (replaces MPI_Allreduce(LAND), M:255)
+            if (h0->allreduce && h0->allreduce(&r, h0->allreduce_ctx) != 0)
+                return fail(HEAT_E_PEER, "heat_run: allreduce callback failed");
+            if (r < h0->p.conv_eps) conv = 1; // M:245 / C:67
+        }
+    }
+    float ms = 0.0f;
+    for (int k = 0; k < n; k++) {
+        CK(cudaSetDevice(hs[k]->p.device));
+        CK(cudaEventRecord(hs[k]->ev1, hs[k]->stream));
+    }
+    for (int k = 0; k < n; k++) {
+        int rc = heat_sync(hs[k]);
+        if (rc) return rc;
+        float t = 0.0f;
+        CK(cudaEventElapsedTime(&t, hs[k]->ev0, hs[k]->ev1));
+        ms = fmaxf(ms, t);
+    }
+    for (int k = 0; k < n; k++) hs[k]->last_ms = ms;
+    if (updates_done) *updates_done = (int)done;
+    if (converged) *converged = conv;
+    return HEAT_OK;
+}
+
+extern "C" int heat_run(heat_handle* h, int steps, int* updates_done, int* converged)
+{
+    if (!h) return fail(HEAT_E_INVALID, "heat_run: null handle");
+    if (h->local_nb[0] || h->local_nb[1]) return fail(HEAT_E_STATE, "heat_run: locally connected strips run through heat_group_run");
+    if (h->p.nranks > 1 && h->p.conv_every > 0 && !h->allreduce)
+        return fail(HEAT_E_STATE, "heat_run: strips in several processes need heat_set_allreduce_max for the convergence check");
+    return heat_group_run(&h, 1, steps, updates_done, converged);
+}
+
+extern "C" int heat_elapsed_ms(heat_handle* h, float* ms)
+{
+    if (!h || !ms) return fail(HEAT_E_INVALID, "heat_elapsed_ms: bad arguments");
+    *ms = h->last_ms;
+    return HEAT_OK;
+}
+
+extern "C" int heat_launch_count(heat_handle* h, int64_t* launches)
+{
+    if (!h || !launches) return fail(HEAT_E_INVALID, "heat_launch_count: bad arguments");
+    *launches = h->launches;
+    return HEAT_OK;
+}
+
+extern "C" int heat_residual(heat_handle* h, float* residual)
+{
+    if (!h || !residual) return fail(HEAT_E_INVALID, "heat_residual: bad arguments");
+    CK(cudaSetDevice(h->p.device));
+    CK(cudaMemsetAsync(h->d_resid, 0, sizeof(unsigned), h->stream));
+    if (h->nloc >= 3 && h->p.ny >= 3) {
+        heat_absdiff_max<<<h->sm_count * 8, 256, 0, h->stream>>>(h->buf[0], h->buf[1], h->nloc, h->p.ny, h->pitch, h->d_resid);
+        h->launches++;
+        CK(cudaGetLastError());
+    }
+    CK(cudaMemcpyAsync(h->h_resid, h->d_resid, sizeof(unsigned), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    memcpy(residual, h->h_resid, sizeof(float));
+    return HEAT_OK;
+}
+
+// ------------------------------------------------------------------ data movement
+extern "C" int heat_set_halo_mode(heat_handle* h, int mode)
+{
+    if (!h || (mode != HEAT_HALO_P2P && mode != HEAT_HALO_EXTERNAL)) return fail(HEAT_E_INVALID, "heat_set_halo_mode: bad arguments");
+    h->external_halo = (mode == HEAT_HALO_EXTERNAL);
+    return HEAT_OK;
+}
+
+static int after_upload(heat_handle* h)
+{
+    h->cur = 0;
+    h->it = 0;
+    // an upload counts as one epoch of the strip flags: neighbours may not store into this
+    // strip's ghost rows before the upload has landed
+    h->seq++;
+    const bool has_n = h->p.rank > 0, has_s = h->p.rank < h->p.nranks - 1;
+    if ((has_n || has_s) && h->connected && !h->external_halo) {
+        if (h->local_nb[0] || h->local_nb[1]) {
+            CK(cudaEventRecord(h->ev_done[h->seq & 1], h->stream));
+        } else {
+            heat_signal<<<1, 32, 0, h->stream>>>(has_n ? h->peer[0].flag : nullptr, has_s ? h->peer[1].flag : nullptr, h->seq);
+            h->launches++;
+            CK(cudaGetLastError());
+        }
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    return HEAT_OK;
+}
+
+static int upload_from(heat_handle* h, const void* src, cudaMemcpyKind kind)
+{
+    if (!h || !src) return fail(HEAT_E_INVALID, "heat_upload: bad arguments");
+    if ((h->p.rank > 0 || h->p.rank < h->p.nranks - 1) && !h->connected && !h->external_halo)
+        return fail(HEAT_E_STATE, "heat_upload: connect the strips first");
+    CK(cudaSetDevice(h->p.device));
+    const float* rows = (const float*)src + (size_t)h->lo * h->p.ny;
+    for (int b = 0; b < 2; b++) // C:197-198: the initial field goes into both buffers
+        CK(cudaMemcpy2DAsync(h->buf[b], h->pitch * sizeof(float), rows, (size_t)h->p.ny * sizeof(float),
+                             (size_t)h->p.ny * sizeof(float), h->nloc, kind, h->stream));
+    return after_upload(h);
+}
+
+extern "C" int heat_upload(heat_handle* h, const float* full_grid) { return upload_from(h, full_grid, cudaMemcpyHostToDevice); }
+extern "C" int heat_upload_device(heat_handle* h, const void* d_full_grid) { return upload_from(h, d_full_grid, cudaMemcpyDeviceToDevice); }
+
+extern "C" int heat_init_inidat(heat_handle* h)
+{
+    if (!h) return fail(HEAT_E_INVALID, "heat_init_inidat: null handle");
+    if ((h->p.rank > 0 || h->p.rank < h->p.nranks - 1) && !h->connected && !h->external_halo)
+        return fail(HEAT_E_STATE, "heat_init_inidat: connect the strips first");
+    CK(cudaSetDevice(h->p.device));
+    heat_inidat_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(h->buf[0], h->buf[1], h->p.nx, h->p.ny, h->lo, h->nloc, h->pitch);
+    h->launches++;
+    CK(cudaGetLastError());
+    return after_upload(h);
+}
+
+extern "C" int heat_download(heat_handle* h, float* full_grid)
+{
+    if (!h || !full_grid) return fail(HEAT_E_INVALID, "heat_download: bad arguments");
+    CK(cudaSetDevice(h->p.device));
+    // only the rows this strip owns (ghost rows belong to the neighbours)
+    const int first = h->row0 - h->lo;
+    CK(cudaMemcpy2DAsync(full_grid + (size_t)h->row0 * h->p.ny, (size_t)h->p.ny * sizeof(float),
+                         h->buf[h->cur] + (size_t)first * h->pitch, h->pitch * sizeof(float),
+                         (size_t)h->p.ny * sizeof(float), h->rows_own, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return HEAT_OK;
+}
+
+extern "C" int heat_device_view(heat_handle* h, int which, void** d_ptr, int64_t* pitch, int* local_rows, int* first_global_row)
+{
+    if (!h || (which != 0 && which != 1)) return fail(HEAT_E_INVALID, "heat_device_view: bad arguments");
+    if (d_ptr) *d_ptr = h->buf[which == 0 ? h->cur : 1 - h->cur];
+    if (pitch) *pitch = h->pitch;
+    if (local_rows) *local_rows = h->nloc;
+    if (first_global_row) *first_global_row = h->lo;
+    return HEAT_OK;
+}
+
+// ------------------------------------------------------------------ one-shot (C:176-242)
+extern "C" int heat_solve(const heat_params* p, float* grid, int* updates_done, int* converged)
+{
+    if (!grid) return fail(HEAT_E_INVALID, "heat_solve: null grid");
+    if (p && p->nranks != 1) return fail(HEAT_E_INVALID, "heat_solve: one strip only (use the handle API for strips)");
+    heat_handle* h = nullptr;
+    int rc = heat_create(p, &h);
+    if (rc) return rc;
+    rc = heat_upload(h, grid);
+    if (!rc) rc = heat_run(h, p->steps, updates_done, converged);
+    if (!rc) rc = heat_download(h, grid);
+    heat_destroy(h);
+    return rc;
+}
+
+// ------------------------------------------------------------------ stateless updates (C:140-163, C:42-138)
+template <bool RESID>
+static int step_device(const void* d_in, void* d_out, int nx, int ny, float cx, float cy, int arith, unsigned* resid, void* stream)
+{
+    if (!d_in || !d_out || nx < 1 || ny < 1 || arith < 0 || arith > 2 || (RESID && !resid))
+        return fail(HEAT_E_INVALID, "heat_step_device: bad arguments");
+    if (nx < 3 || ny < 3) return HEAT_OK;
+    dim3 grid((unsigned)((ny - 2 + 255) / 256), (unsigned)min(nx - 2, 148 * 8));
+    const float* in = (const float*)d_in;
+    float* out = (float*)d_out;
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (arith) {
+    case 0: heat_step_generic<0, RESID><<<grid, 256, 0, st>>>(in, out, nx, ny, ny, ny, cx, cy, resid, nullptr, nullptr); break;
+    case 1: heat_step_generic<1, RESID><<<grid, 256, 0, st>>>(in, out, nx, ny, ny, ny, cx, cy, resid, nullptr, nullptr); break;
+    default: heat_step_generic<2, RESID><<<grid, 256, 0, st>>>(in, out, nx, ny, ny, ny, cx, cy, resid, nullptr, nullptr); break;
+    }
+    CK(cudaGetLastError());
+    return HEAT_OK;
+}
+
+extern "C" int heat_step_device(const void* d_in, void* d_out, int nx, int ny, float cx, float cy, int arith, void* stream)
+{
+    return step_device<false>(d_in, d_out, nx, ny, cx, cy, arith, nullptr, stream);
+}
+
+extern "C" int heat_step_residual_device(const void* d_in, void* d_out, int nx, int ny, float cx, float cy, int arith,
+                                         void* d_residual_bits, void* stream)
+{
+    return step_device<true>(d_in, d_out, nx, ny, cx, cy, arith, (unsigned*)d_residual_bits, stream);
+}
+
+// ------------------------------------------------------------------ neighbours
+static int ptr_offset(const void* p, int64_t* off)
+{
+    // small cudaMalloc blocks are sub-allocated; an IPC handle exports the whole underlying
+    // allocation, so the importer needs the offset.  The driver entry point is fetched at run
+    // time so that the library has no link-time dependency on libcuda.so.1.
+    typedef CUresult (*range_fn)(CUdeviceptr*, size_t*, CUdeviceptr);
+    static range_fn get_range = nullptr;
+    if (!get_range) {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        CK(cudaGetDriverEntryPoint("cuMemGetAddressRange", &f, cudaEnableDefault, &q));
+        if (!f || q != cudaDriverEntryPointSuccess) return fail(HEAT_E_CUDA, "cuMemGetAddressRange not available");
+        get_range = (range_fn)f;
+    }
+    CUdeviceptr base = 0;
+    size_t size = 0;
+    CUresult r = get_range(&base, &size, (CUdeviceptr)p);
+    if (r != CUDA_SUCCESS) return fail(HEAT_E_CUDA, "cuMemGetAddressRange failed (%d)", (int)r);
+    *off = (int64_t)((CUdeviceptr)p - base);
+    return HEAT_OK;
+}
+
+extern "C" int heat_ipc_export(heat_handle* h, void* blob, size_t blob_bytes)
+{
+    if (!h || !blob || blob_bytes < sizeof(ipc_blob)) return fail(HEAT_E_INVALID, "heat_ipc_export: bad arguments");
+    CK(cudaSetDevice(h->p.device));
+    ipc_blob b;
+    memset(&b, 0, sizeof b);
+    memcpy(b.magic, "HEATIPC1", 8);
+    void* ptrs[3] = {h->buf[0], h->buf[1], h->flags};
+    for (int k = 0; k < 3; k++) {
+        CK(cudaIpcGetMemHandle(&b.mem[k], ptrs[k]));
+        int rc = ptr_offset(ptrs[k], &b.offset[k]);
+        if (rc) return rc;
+    }
+    b.nloc = h->nloc;
+    b.rank = h->p.rank;
+    b.nranks = h->p.nranks;
+    b.pitch = h->pitch;
+    memset(blob, 0, blob_bytes);
+    memcpy(blob, &b, sizeof b);
+    return HEAT_OK;
+}
+
+static int open_side(heat_handle* h, int side, const void* blob)
+{
+    ipc_blob b;
+    memcpy(&b, blob, sizeof b);
+    if (memcmp(b.magic, "HEATIPC1", 8) != 0) return fail(HEAT_E_INVALID, "heat_ipc_connect: not an export blob");
+    const int want = h->p.rank + (side == 0 ? -1 : 1);
+    if (b.rank != want || b.nranks != h->p.nranks || b.pitch != h->pitch)
+        return fail(HEAT_E_PEER, "heat_ipc_connect: blob is strip %d/%d pitch %lld, expected strip %d/%d pitch %lld", b.rank,
+                    b.nranks, (long long)b.pitch, want, h->p.nranks, (long long)h->pitch);
+    void* base[3];
+    for (int k = 0; k < 3; k++) {
+        cudaError_t e = cudaIpcOpenMemHandle(&base[k], b.mem[k], cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) return fail(HEAT_E_PEER, "cudaIpcOpenMemHandle failed: %s", cudaGetErrorString(e));
+        h->peer[side].ipc_base[k] = base[k];
+    }
+    h->peer[side].buf[0] = (float*)((char*)base[0] + b.offset[0]);
+    h->peer[side].buf[1] = (float*)((char*)base[1] + b.offset[1]);
+    // the neighbour's slot for messages from its south side is [1], from its north side [0]
+    unsigned long long* f = (unsigned long long*)((char*)base[2] + b.offset[2]);
+    h->peer[side].flag = (side == 0) ? &f[1] : &f[0];
+    h->peer[side].nloc = b.nloc;
+    return HEAT_OK;
+}
+
+extern "C" int heat_ipc_connect(heat_handle* h, const void* north_blob, const void* south_blob)
+{
+    if (!h) return fail(HEAT_E_INVALID, "heat_ipc_connect: null handle");
+    const bool has_n = h->p.rank > 0, has_s = h->p.rank < h->p.nranks - 1;
+    if (has_n != (north_blob != nullptr) || has_s != (south_blob != nullptr))
+        return fail(HEAT_E_PEER, "heat_ipc_connect: strip %d of %d needs north=%d south=%d", h->p.rank, h->p.nranks, has_n, has_s);
+    CK(cudaSetDevice(h->p.device));
+    int rc = HEAT_OK;
+    if (has_n) rc = open_side(h, 0, north_blob);
+    if (!rc && has_s) rc = open_side(h, 1, south_blob);
+    if (rc) return rc;
+    h->connected = true;
+    return HEAT_OK;
+}
+
+extern "C" int heat_connect_local(heat_handle* h, heat_handle* north, heat_handle* south)
+{
+    if (!h) return fail(HEAT_E_INVALID, "heat_connect_local: null handle");
+    const bool has_n = h->p.rank > 0, has_s = h->p.rank < h->p.nranks - 1;
+    if (has_n != (north != nullptr) || has_s != (south != nullptr))
+        return fail(HEAT_E_PEER, "heat_connect_local: strip %d of %d needs north=%d south=%d", h->p.rank, h->p.nranks, has_n, has_s);
+    CK(cudaSetDevice(h->p.device));
+    heat_handle* nb[2] = {north, south};
+    for (int side = 0; side < 2; side++) {
+        heat_handle* o = nb[side];
+        if (!o) continue;
+        if (o->p.rank != h->p.rank + (side ? 1 : -1) || o->p.nranks != h->p.nranks || o->pitch != h->pitch)
+            return fail(HEAT_E_PEER, "heat_connect_local: neighbour on side %d is strip %d, not adjacent", side, o->p.rank);
+        if (o->p.device != h->p.device) {
+            int can = 0;
+            CK(cudaDeviceCanAccessPeer(&can, h->p.device, o->p.device));
+            if (!can) return fail(HEAT_E_PEER, "device %d cannot access device %d", h->p.device, o->p.device);
+            cudaError_t e = cudaDeviceEnablePeerAccess(o->p.device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+                return fail(HEAT_E_PEER, "cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+            cudaGetLastError();
+        }
+        h->peer[side].buf[0] = o->buf[0];
+        h->peer[side].buf[1] = o->buf[1];
+        h->peer[side].flag = (side == 0) ? &o->flags[1] : &o->flags[0];
+        h->peer[side].nloc = o->nloc;
+        h->local_nb[side] = o;
+    }
+    h->connected = true;
+    return HEAT_OK;
+}

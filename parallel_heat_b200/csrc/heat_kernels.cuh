@@ -1,0 +1,273 @@
+// heat_kernels.cuh -- sm_100a kernels of the solver loop.
+//
+// Reference regions replaced (M = mpi/mpi_heat_improved_persistent_stat.c,
+// C = cuda/cuda_heat.cu; nothing here is derived from their code):
+//   K0 heat_inidat_kernel     inidat                    M:315-321 / C:274-280
+//   K1 heat_step_vec<..,0>    stencil update            M:162-234 / C:140-163
+//   K2 heat_step_vec<..,1>    update + convergence      C:42-138 + C:32-40, M:236-261
+//   K1g heat_step_generic     same update, any pitch/alignment (small or odd grids)
+//   K3 (in K1/K2)             first/last owned row also stored into the neighbour
+//                             strip's ghost row (replaces MPI halo requests M:130-155)
+//   heat_signal/heat_wait     step flags between strips (replaces Startall/Waitall M:160-177,263)
+//
+// All three arithmetic modes are written with explicit rounding intrinsics, so the
+// result does not depend on -fmad.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define HEAT_ARITH_F32_FMA 0
+#define HEAT_ARITH_F32_NOFMA 1
+#define HEAT_ARITH_F64MIX 2
+
+namespace heatk {
+
+// ------------------------------------------------------------------ arithmetic
+// new = u + cx*((S+N) - 2u) + cy*((E+W) - 2u), evaluation order of M:168-174 / C:155-161.
+template <int ARITH>
+__device__ __forceinline__ float upd(float c, float n, float s, float e, float w, float cx, float cy)
+{
+    if constexpr (ARITH == HEAT_ARITH_F32_FMA) {
+        // what nvcc makes of C:155-161 by default: 5 FADD + 2 FFMA (2u is exact)
+        float t1 = __fsub_rn(__fadd_rn(s, n), __fadd_rn(c, c));
+        float t2 = __fsub_rn(__fadd_rn(e, w), __fadd_rn(c, c));
+        return __fmaf_rn(cy, t2, __fmaf_rn(cx, t1, c));
+    } else if constexpr (ARITH == HEAT_ARITH_F32_NOFMA) {
+        // C:155-161 with -fmad=false: every product and sum rounded to float
+        float t1 = __fsub_rn(__fadd_rn(s, n), __fadd_rn(c, c));
+        float t2 = __fsub_rn(__fadd_rn(e, w), __fadd_rn(c, c));
+        return __fadd_rn(__fadd_rn(c, __fmul_rn(cx, t1)), __fmul_rn(cy, t2));
+    } else {
+        // M:168-174: float neighbour sums, then double (literal 2.0, promoted cx/cy), one final rounding
+        double cd = (double)c;
+        double c2 = __dadd_rn(cd, cd);
+        double t1 = __dsub_rn((double)__fadd_rn(s, n), c2);
+        double t2 = __dsub_rn((double)__fadd_rn(e, w), c2);
+        double r = __dadd_rn(__dadd_rn(cd, __dmul_rn((double)cx, t1)), __dmul_rn((double)cy, t2));
+        return __double2float_rn(r);
+    }
+}
+
+__device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+
+// ------------------------------------------------------------------ K0 inidat
+// (float)(ix*(nx-ix-1)*iy*(ny-iy-1)) with the int32 wrap of the reference (M:320).
+// Local array = global rows [row_lo, row_lo+nloc); writes both buffers (C:197-198).
+__global__ void heat_inidat_kernel(float* __restrict__ a, float* __restrict__ b, int nx, int ny, int row_lo,
+                                   int nloc, int64_t pitch)
+{
+    const int64_t total = (int64_t)nloc * pitch;
+    for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
+        const int lr = (int)(k / pitch);
+        const int iy = (int)(k - (int64_t)lr * pitch);
+        const int ix = row_lo + lr;
+        float v = 0.0f;
+        if (iy < ny) {
+            uint32_t p = (uint32_t)ix * (uint32_t)(nx - ix - 1) * (uint32_t)iy * (uint32_t)(ny - iy - 1);
+            v = (float)(int32_t)p;
+        }
+        a[k] = v;
+        b[k] = v;
+    }
+}
+
+// ------------------------------------------------------------------ residual helpers
+// non-negative floats order like their bit patterns, so max|d| is an integer max
+__device__ __forceinline__ void block_max_to_global(float m, unsigned* gmax)
+{
+    unsigned bits = __reduce_max_sync(0xffffffffu, __float_as_uint(m));
+    __shared__ unsigned smax[32];
+    const int warp = threadIdx.x >> 5, nwarp = (blockDim.x + 31) >> 5;
+    if ((threadIdx.x & 31) == 0) smax[warp] = bits;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned v = (threadIdx.x < nwarp) ? smax[threadIdx.x] : 0u;
+        v = __reduce_max_sync(0xffffffffu, v);
+        if (threadIdx.x == 0 && v != 0u) atomicMax(gmax, v);
+    }
+}
+
+// ------------------------------------------------------------------ K1g generic
+// One thread per point, lanes along iy (coalesced).  Any ny, any pitch, unaligned bases.
+// Ring is not written.  Used for odd shapes and by the stateless entry points.
+template <int ARITH, bool RESID>
+__global__ void __launch_bounds__(256)
+heat_step_generic(const float* __restrict__ in, float* __restrict__ out, int nrows, int ny, int64_t pitch_in,
+                  int64_t pitch_out, float cx, float cy, unsigned* __restrict__ resid, float* peer_n, float* peer_s)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x + 1;
+    float m = 0.0f;
+    if (j < ny - 1) {
+        for (int i = blockIdx.y + 1; i < nrows - 1; i += gridDim.y) {
+            const float* c = in + (int64_t)i * pitch_in + j;
+            const float cv = c[0];
+            const float o = upd<ARITH>(cv, c[-pitch_in], c[pitch_in], c[1], c[-1], cx, cy);
+            out[(int64_t)i * pitch_out + j] = o;
+            if (i == 1 && peer_n) peer_n[j] = o;
+            if (i == nrows - 2 && peer_s) peer_s[j] = o;
+            if (RESID) m = fmaxf(m, fabsf(__fsub_rn(cv, o)));
+        }
+    }
+    if (RESID) block_max_to_global(m, resid);
+}
+
+// ------------------------------------------------------------------ K1/K2 vector row streaming
+// Each thread owns 4 consecutive columns (one float4) and walks down `rows_per_tile`
+// rows keeping the N / C / S rows in registers: per row one LDG.128, one STG.128, two
+// shuffles for the E/W neighbours inside the warp and one predicated 4-byte load on lanes
+// 0 and 31 for the neighbours across the warp edge.  Requirements: pitch % 4 == 0, base
+// 16-byte aligned, columns [ny, pitch) are padding.  Ring columns (0 and ny-1) are written
+// back unchanged: both buffers always hold the same ring, so this equals "not written".
+//   grid.x = ceil(pitch/4 / THREADS), grid.y = number of row tiles, block = THREADS
+//   reverse != 0 walks the tiles bottom-up (alternate sweeps re-use what is left in L2).
+template <int ARITH, bool RESID, int THREADS, int UNROLL>
+__global__ void __launch_bounds__(THREADS)
+heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int nrows, int ny, int64_t pitch,
+              int rows_per_tile, float cx, float cy, unsigned* __restrict__ resid, float* peer_n, float* peer_s,
+              int reverse)
+{
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int npitch = (int)pitch;
+    int col = (blockIdx.x * THREADS + threadIdx.x) * 4;
+    // whole warp beyond the row: nothing to do (warp-uniform exit, before any shuffle)
+    if (col - lane * 4 >= npitch) {
+        if (RESID) block_max_to_global(0.0f, resid);
+        return;
+    }
+    const bool live = col < npitch;
+    if (!live) col = npitch - 4; // keep the lane in bounds for loads; it never stores
+
+    const int ntiles = gridDim.y;
+    const int tile = reverse ? (ntiles - 1 - (int)blockIdx.y) : (int)blockIdx.y;
+    const int r0 = 1 + tile * rows_per_tile;
+    const int r1 = min(r0 + rows_per_tile, nrows - 1);
+
+    // which of my 4 columns are ring / padding (copied through, never updated)
+    const bool kx = (col == 0) || (col >= ny - 1);
+    const bool ky = (col + 1 >= ny - 1);
+    const bool kz = (col + 2 >= ny - 1);
+    const bool kw = (col + 3 >= ny - 1);
+    // neighbours across the warp edge: lane 0 needs col-1, lane 31 needs col+4
+    const bool edge_lane = (lane == 0 && col > 0) || (lane == 31 && col + 4 < npitch);
+    const int edge_off = (lane == 0) ? -1 : 4;
+
+    const float* p = in + (int64_t)(r0 - 1) * pitch + col;
+    float* q = out + (int64_t)r0 * pitch + col;
+    float4 n = ld4(p);
+    float4 c = ld4(p + pitch);
+    float ec = edge_lane ? p[pitch + edge_off] : 0.0f;
+    p += 2 * pitch; // points at row r+1 (the S row of the first output row)
+    float m = 0.0f;
+
+    for (int r = r0; r < r1; r += UNROLL) {
+        float4 s[UNROLL];
+        float es[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; u++) {
+            // rows past the tile are clamped to its last S row: loaded but never used for a store
+            const int64_t off = (int64_t)min(u, r1 - 1 - r) * pitch;
+            s[u] = ld4(p + off);
+            es[u] = edge_lane ? p[off + edge_off] : 0.0f;
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; u++) {
+            if (r + u < r1) {
+                float wl = __shfl_up_sync(FULL, c.w, 1);
+                float er = __shfl_down_sync(FULL, c.x, 1);
+                if (lane == 0) wl = ec;
+                if (lane == 31) er = ec;
+                float4 o;
+                o.x = upd<ARITH>(c.x, n.x, s[u].x, c.y, wl, cx, cy);
+                o.y = upd<ARITH>(c.y, n.y, s[u].y, c.z, c.x, cx, cy);
+                o.z = upd<ARITH>(c.z, n.z, s[u].z, c.w, c.y, cx, cy);
+                o.w = upd<ARITH>(c.w, n.w, s[u].w, er, c.z, cx, cy);
+                if (kx) o.x = c.x;
+                if (ky) o.y = c.y;
+                if (kz) o.z = c.z;
+                if (kw) o.w = c.w;
+                if (live) {
+                    st4(q, o);
+                    if (r + u == 1 && peer_n) st4(peer_n + col, o);
+                    if (r + u == nrows - 2 && peer_s) st4(peer_s + col, o);
+                }
+                if (RESID) {
+                    m = fmaxf(m, fabsf(__fsub_rn(c.x, o.x)));
+                    m = fmaxf(m, fabsf(__fsub_rn(c.y, o.y)));
+                    m = fmaxf(m, fabsf(__fsub_rn(c.z, o.z)));
+                    m = fmaxf(m, fabsf(__fsub_rn(c.w, o.w)));
+                }
+                n = c;
+                c = s[u];
+                ec = es[u];
+                q += pitch;
+            }
+        }
+        p += (int64_t)UNROLL * pitch;
+    }
+    if (RESID) block_max_to_global(live ? m : 0.0f, resid);
+}
+
+// ------------------------------------------------------------------ residual of two buffers
+// max |a-b| over the interior of a strip (heat_residual(): a separate pass, not on the hot path)
+__global__ void __launch_bounds__(256)
+heat_absdiff_max(const float* __restrict__ a, const float* __restrict__ b, int nrows, int ny, int64_t pitch,
+                 unsigned* __restrict__ resid)
+{
+    float m = 0.0f;
+    const int64_t total = (int64_t)(nrows - 2) * pitch;
+    for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
+        const int lr = (int)(k / pitch);
+        const int iy = (int)(k - (int64_t)lr * pitch);
+        if (iy < ny) {
+            const int64_t idx = k + pitch; // skip local row 0
+            m = fmaxf(m, fabsf(__fsub_rn(a[idx], b[idx])));
+        }
+    }
+    block_max_to_global(m, resid);
+}
+
+// ------------------------------------------------------------------ strip flags
+// After update u completes, a strip writes u+1 into each neighbour's flag slot
+// (system-scope release: its ghost-row stores are visible before the flag).
+__global__ void heat_signal(unsigned long long* peer_flag_n, unsigned long long* peer_flag_s, unsigned long long value)
+{
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        if (peer_flag_n) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peer_flag_n), "l"(value) : "memory");
+        if (peer_flag_s) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peer_flag_s), "l"(value) : "memory");
+    }
+}
+
+// Before update u+1 a strip waits until both neighbours have finished update u.
+// Bounded: after timeout_ns the kernel gives up and raises *status (checked by the host).
+__global__ void heat_wait(const unsigned long long* flag_n, const unsigned long long* flag_s, unsigned long long value,
+                          unsigned long long timeout_ns, int* status)
+{
+    if (threadIdx.x != 0) return;
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (int side = 0; side < 2; side++) {
+        const unsigned long long* f = side ? flag_s : flag_n;
+        if (!f) continue;
+        unsigned spins = 0;
+        for (;;) {
+            unsigned long long v;
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+            if (v >= value) break;
+            if ((++spins & 1023u) == 0) {
+                unsigned long long t;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                if (t - t0 > timeout_ns) {
+                    *status = 1;
+                    __threadfence_system();
+                    return;
+                }
+            }
+            __nanosleep(64);
+        }
+    }
+}
+
+} // namespace heatk

@@ -1,0 +1,185 @@
+"""Row strips across GPUs, one process per GPU (torchrun), torch.distributed as plumbing.
+
+Replaces the reference's 2-D cartesian block decomposition and persistent halo
+requests (mpi/mpi_heat_improved_persistent_stat.c:51-84,100-127,130-155,160-161,
+177,263,270-297) with a G x 1 row-strip split inside one NVSwitch box:
+
+  halo="p2p"      (default, the product path) every rank exports its buffers with CUDA
+                  IPC; the update kernel stores a strip's first/last owned row straight
+                  into the neighbour's ghost row over NVLink and step flags order the
+                  strips on the device -- no host work per update, no collective.
+  halo="sendrecv" the ghost rows travel as torch.distributed P2P ops (NCCL on GPUs, gloo
+                  on CPUs) between updates; the portable fallback and the cross-check.
+
+The convergence check is one 4-byte max-allreduce every conv_every updates
+(replaces MPI_Allreduce(LAND), M:255).  torch.distributed is only used for the
+blob exchange, barriers, that allreduce and the final gather.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import api
+
+
+def partition(nx, nranks):
+    """[(row0, rows)] per rank -- heat_strip_rows for every rank."""
+    return [api.strip_rows(nx, nranks, r) for r in range(nranks)]
+
+
+def local_window(nx, nranks, rank):
+    """Global rows [lo, hi) a strip keeps: its own rows plus one ghost row per neighbour."""
+    r0, n = api.strip_rows(nx, nranks, rank)
+    lo = r0 - 1 if rank > 0 else 0
+    hi = r0 + n + 1 if rank < nranks - 1 else nx
+    return lo, hi
+
+
+class _CudaRows:
+    """torch views of single rows of a strip's device buffer (for halo='sendrecv')."""
+
+    def __init__(self, solver):
+        self.solver = solver
+
+    def row(self, which, local_row):
+        import torch
+        ptr, pitch, rows, _ = self.solver.device_view(which)
+        ny = self.solver.params.ny
+
+        class _Arr:  # minimal __cuda_array_interface__ holder
+            pass
+        a = _Arr()
+        a.__cuda_array_interface__ = {"shape": (ny,), "typestr": "<f4", "version": 3,
+                                      "data": (ptr + 4 * pitch * local_row, False)}
+        return torch.as_tensor(a, device=f"cuda:{self.solver.params.device}")
+
+
+class StripSolver:
+    """The solver loop of one strip; every rank of the process group makes one.
+
+    solver_cls / rows_cls exist so that the CPU test (gloo, world_size 2) can drive this
+    very class with an oracle-backed stand-in; the product always uses the defaults.
+    """
+
+    def __init__(self, nx, ny, *, group=None, device=None, halo="p2p", solver_cls=None, rows_cls=None, **params):
+        import torch.distributed as dist
+        self.dist = dist
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        if halo not in ("p2p", "sendrecv"):
+            raise ValueError("halo must be 'p2p' or 'sendrecv'")
+        self.halo = halo if self.world > 1 else "none"
+        self.nx, self.ny = nx, ny
+        if device is None:
+            device = 0
+        self.device = device
+        cls = solver_cls or api.HeatSolver
+        self.solver = cls(nx, ny, rank=self.rank, nranks=self.world, device=device, **params)
+        self.row0, self.rows = api.strip_rows(nx, self.world, self.rank)
+        self.lo, self.hi = local_window(nx, self.world, self.rank)
+        self.nloc = self.hi - self.lo
+        self.conv_every = int(self.solver.params.conv_every)
+        self._rows = (rows_cls or _CudaRows)(self.solver)
+        if self.halo == "p2p":
+            self._connect_p2p()
+        elif self.halo == "sendrecv":
+            self.solver.set_halo_mode(api.HALO_EXTERNAL)
+            if solver_cls is None:
+                # NCCL P2P ops are ordered against torch's current stream: run the updates there too
+                import torch
+                self.solver.set_stream(torch.cuda.current_stream(device).cuda_stream)
+        if self.world > 1:
+            self.solver.set_allreduce_max(self._allreduce_max)
+
+    # ------------------------------------------------------------------ wiring
+    def _connect_p2p(self):
+        blobs = [None] * self.world
+        self.dist.all_gather_object(blobs, self.solver.ipc_export(), group=self.group)
+        north = blobs[self.rank - 1] if self.rank > 0 else None
+        south = blobs[self.rank + 1] if self.rank < self.world - 1 else None
+        self.solver.ipc_connect(north, south)
+        self.dist.barrier(group=self.group)
+
+    def _allreduce_max(self, value):
+        import torch
+        dev = "cpu" if self.dist.get_backend(self.group) == "gloo" else f"cuda:{self.device}"
+        t = torch.tensor([value], dtype=torch.float32, device=dev)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
+        return float(t.item())
+
+    # ------------------------------------------------------------------ data
+    def upload(self, full_grid):
+        self.solver.upload(full_grid)
+        if self.world > 1:
+            self.dist.barrier(group=self.group)
+
+    def init_inidat(self):
+        self.solver.init_inidat()
+        if self.world > 1:
+            self.dist.barrier(group=self.group)
+
+    def _exchange(self):
+        """halo='sendrecv': newest buffer, first/last owned row -> neighbours' ghost rows."""
+        dist = self.dist
+        ops = []
+        if self.rank > 0:
+            ops.append(dist.P2POp(dist.isend, self._rows.row(0, 1), self.rank - 1, self.group))
+            ops.append(dist.P2POp(dist.irecv, self._rows.row(0, 0), self.rank - 1, self.group))
+        if self.rank < self.world - 1:
+            ops.append(dist.P2POp(dist.isend, self._rows.row(0, self.nloc - 2), self.rank + 1, self.group))
+            ops.append(dist.P2POp(dist.irecv, self._rows.row(0, self.nloc - 1), self.rank + 1, self.group))
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+
+    # ------------------------------------------------------------------ time loop
+    def enqueue(self, updates):
+        """`updates` plain updates, asynchronous where the transport allows it."""
+        if self.halo == "sendrecv":
+            for _ in range(updates):
+                self.solver.enqueue(1)
+                self._exchange()
+        else:
+            self.solver.enqueue(updates)
+
+    def sync(self):
+        self.solver.sync()
+
+    def run(self, steps):
+        """The whole loop (M:159-265): returns (updates_done, converged), same on every rank."""
+        if self.halo != "sendrecv":
+            return self.solver.run(steps)
+        # host-driven exchange: same loop structure as heat_group_run, one update at a time
+        p = self.solver.params
+        total = steps + (1 if p.step_convention == api.STEPS_MPI else 0)
+        done, conv, it = 0, False, getattr(self, "_it", 0)
+        K = self.conv_every
+        while done < total and not conv:
+            check = K > 0 and ((it % K == 0) if p.conv_phase == api.PHASE_CUDA else ((it + 1) % K == 0))
+            self.solver.enqueue(1)
+            if check:
+                r = self._allreduce_max(self.solver.residual())
+                conv = r < p.conv_eps
+            self._exchange()
+            done += 1
+            it += 1
+        self._it = it
+        self.solver.sync()
+        return done, conv
+
+    # ------------------------------------------------------------------ result
+    def gather(self, dst=0):
+        """Newest field assembled on rank `dst` (replaces the END messages, M:270-297)."""
+        mine = np.zeros((self.nx, self.ny), np.float32)
+        self.solver.download(mine)
+        part = np.ascontiguousarray(mine[self.row0:self.row0 + self.rows])
+        if self.world == 1:
+            return mine
+        parts = [None] * self.world if self.rank == dst else None
+        self.dist.gather_object(part, parts, dst=dst, group=self.group)
+        if self.rank != dst:
+            return None
+        return np.concatenate(parts, axis=0)
+
+    def close(self):
+        self.solver.close()
