@@ -1,0 +1,370 @@
+#!/usr/bin/env python3
+"""bench.py -- the solver-loop benchmark (BASELINE.json metric: GLUP/s and % of HBM roofline).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A bench "step" is ONE Jacobi update of the whole grid (one pass of the hot path).
+Workloads (BASELINE.json configs):
+    c2      (default)  8192 x 8192 float32, no convergence check; at N GPUs the grid is
+                       (8192*N) x 8192 cut into N row strips (weak scaling of config[1])
+    c3                 16384 x 16384 with the convergence check every 20 updates (1 GPU)
+    strong             65536 x 65536 row strips over N GPUs (config[3])
+    weak32k            (32768*N) x 32768, temporal_block 4 (config[4])
+    c1                 1024 x 1024 (config[0]'s grid; a parity case, here only for curiosity)
+`value` = LUPs of all ranks / device time (CUDA events on the launching stream, max over
+ranks), inputs resident in HBM.  `e2e` = the same through heat_solve() with HOST buffers
+(H2D + K updates + D2H inside the timed region).  --impl reference times the reference's own
+MPI program (oracle/_ref, unmodified source, OpenMP build, all host cores) on the same grid.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "GLUP/s (5-point Jacobi lattice-point updates per second, solver loop)"
+BYTES_PER_LUP = 8.0  # float32 single-step: 4 B read + 4 B written per point-update
+
+
+def workload(name, n):
+    if name == "c2":
+        return dict(nx=8192 * n, ny=8192, conv_every=0, temporal_block=1, scaling="weak",
+                    text=f"{8192 * n}x8192 float32 inidat field, {n} row strip(s) of 8192 rows, no convergence check")
+    if name == "c3":
+        return dict(nx=16384, ny=16384, conv_every=20, temporal_block=1, scaling="weak",
+                    text="16384x16384 float32 inidat field, convergence check every 20 updates")
+    if name == "strong":
+        return dict(nx=65536, ny=65536, conv_every=0, temporal_block=1, scaling="strong",
+                    text=f"65536x65536 float32 inidat field over {n} row strip(s)")
+    if name == "weak32k":
+        return dict(nx=32768 * n, ny=32768, conv_every=0, temporal_block=4, scaling="weak",
+                    text=f"{32768 * n}x32768 float32 inidat field, {n} strip(s), 4 updates per HBM pass")
+    if name == "c1":
+        return dict(nx=1024, ny=1024, conv_every=0, temporal_block=1, scaling="weak", text="1024x1024 float32 inidat field")
+    raise SystemExit(f"unknown workload {name}")
+
+
+def measured_peak():
+    f = ROOT / "MEASURED_PEAKS.json"
+    if f.exists():
+        try:
+            return float(json.loads(f.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic(name):
+    """Per-launch DRAM bytes of the step kernel from the committed ncu capture, if any."""
+    f = ROOT / "profiles" / "traffic.json"
+    if f.exists():
+        try:
+            return json.loads(f.read_text()).get(name)
+        except Exception:
+            return None
+    return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index=0, period=0.1):
+        self.index, self.period = index, period
+        self.samples, self.reasons = [], set()
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._t = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _once(self):
+        nv = self.nv
+        try:
+            self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+            r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+                     "hw_power_brake_slowdown": 0x80, "sync_boost": 0x10, "applications_clocks_setting": 0x2}
+            for k, bit in names.items():
+                if r & bit:
+                    self.reasons.add(k)
+        except Exception:
+            pass
+
+    def _loop(self):
+        while not self._stop.is_set():
+            self._once()
+            self._stop.wait(self.period)
+
+    def start(self):
+        if self.nv:
+            self._t = threading.Thread(target=self._loop, daemon=True)
+            self._t.start()
+
+    def stop(self):
+        if self._t:
+            self._once()
+            self._stop.set()
+            self._t.join()
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+# ------------------------------------------------------------------------------------ reference arm
+def run_reference_arm(args, wl, rank, world):
+    if rank != 0:
+        return
+    from oracle import pyoracle as O
+    nx, ny = wl["nx"], wl["ny"]
+    cores = os.cpu_count() or 1
+    out = {"metric": METRIC, "unit": "GLUP/s", "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
+           "warmup": args.warmup, "higher_is_better": True, "scaling": wl["scaling"], "vs_baseline": None,
+           "dtype": "f32 grid, f64-mixed arithmetic (M:168-174)", "data": "synthetic",
+           "config": {"workload": wl["text"], "nx": nx, "ny": ny}}
+    exe = O.ref_binary("mpi", nx, ny, conv=wl["conv_every"] > 0, omp=True, opt="O3")
+    lups_per_update = (nx - 2) * (ny - 2)
+    if exe.exists():
+        # bounded sample: a short probe sizes the run to about 20 s of loop time
+        probe = O.run_reference("mpi", nx, ny, 2, conv=wl["conv_every"] > 0, omp=True, opt="O3", capture=False)
+        per_update = max(probe["loop_secs"] / 3, 1e-6)
+        updates = int(max(3, min(args.steps + args.warmup, 20.0 / per_update)))
+        r = O.run_reference("mpi", nx, ny, updates - 1, conv=wl["conv_every"] > 0, omp=True, opt="O3", capture=False)
+        secs, kind = r["loop_secs"], "reference"
+        sample = (f"{updates} updates of {nx}x{ny}: unmodified mpi_heat_improved_persistent_stat.c, -O3 -fopenmp -DOMPCH, "
+                  f"{cores} OpenMP threads, 1-rank MPI stand-in, loop-only time (M:159-265)")
+    else:
+        ini = O.inidat(nx, ny)
+        t0 = time.perf_counter()
+        O.solve(ini, 2, arith=O.MPI_F64MIX)
+        per_update = max((time.perf_counter() - t0) / 2, 1e-6)
+        updates = int(max(3, min(args.steps + args.warmup, 20.0 / per_update)))
+        t0 = time.perf_counter()
+        O.solve(ini, updates, arith=O.MPI_F64MIX)
+        secs, kind = time.perf_counter() - t0, "port"
+        cores = O.threads()
+        sample = f"{updates} updates of {nx}x{ny}: oracle/heat_oracle.c (C restatement, MPI_F64MIX), {cores} OpenMP threads"
+    glups = lups_per_update * updates / secs / 1e9
+    out.update(value=glups, ms_per_step=secs / updates * 1e3,
+               cpu_baseline={"value": glups, "unit": "GLUP/s", "cores": cores, "kind": kind, "sample": sample},
+               e2e={"value": glups, "unit": "GLUP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
+    print(json.dumps(out), flush=True)
+
+
+# ------------------------------------------------------------------------------------ cpu baseline (rank 0, N=1)
+def cpu_baseline(wl):
+    from oracle import pyoracle as O
+    nx, ny = wl["nx"], wl["ny"]
+    cores = os.cpu_count() or 1
+    lups = (nx - 2) * (ny - 2)
+    exe = O.ref_binary("mpi", nx, ny, conv=wl["conv_every"] > 0, omp=True, opt="O3")
+    try:
+        if exe.exists():
+            probe = O.run_reference("mpi", nx, ny, 2, conv=wl["conv_every"] > 0, omp=True, opt="O3", capture=False)
+            updates = int(max(3, min(2000, 15.0 / max(probe["loop_secs"] / 3, 1e-6))))
+            r = O.run_reference("mpi", nx, ny, updates - 1, conv=wl["conv_every"] > 0, omp=True, opt="O3", capture=False)
+            return {"value": lups * updates / r["loop_secs"] / 1e9, "unit": "GLUP/s", "cores": cores, "kind": "reference",
+                    "sample": f"{updates} updates of {nx}x{ny}, unmodified reference MPI source -O3 -fopenmp -DOMPCH, "
+                              f"{cores} threads, loop-only"}
+        ini = O.inidat(nx, ny)
+        t0 = time.perf_counter()
+        O.solve(ini, 2, arith=O.MPI_F64MIX)
+        updates = int(max(3, min(2000, 15.0 / max((time.perf_counter() - t0) / 2, 1e-6))))
+        t0 = time.perf_counter()
+        O.solve(ini, updates, arith=O.MPI_F64MIX)
+        return {"value": lups * updates / (time.perf_counter() - t0) / 1e9, "unit": "GLUP/s", "cores": O.threads(),
+                "kind": "port", "sample": f"{updates} updates of {nx}x{ny}, oracle/heat_oracle.c MPI_F64MIX"}
+    except Exception as e:  # a baseline that cannot run must not take the GPU number down with it
+        return {"value": None, "unit": "GLUP/s", "cores": cores, "kind": "unavailable", "sample": repr(e)[:200]}
+
+
+# ------------------------------------------------------------------------------------ our arm
+def run_ours(args, wl, rank, world, local_rank):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from parallel_heat_b200 import api, build
+    if rank == 0 and build.stale():
+        build.build()
+    if world > 1:
+        dist.barrier()
+    api.load()
+    torch.cuda.set_device(local_rank)
+    nx, ny = wl["nx"], wl["ny"]
+    arith = {"fma": api.F32_FMA, "nofma": api.F32_NOFMA, "f64mix": api.MPI_F64MIX}[args.arith]
+    params = dict(arith=arith, conv_every=wl["conv_every"], temporal_block=wl["temporal_block"])
+    stream = torch.cuda.current_stream()
+
+    if world > 1:
+        from parallel_heat_b200.strips import StripSolver
+        s = StripSolver(nx, ny, device=local_rank, halo=args.halo, **params)
+        solver = s.solver
+        if args.halo == "p2p":
+            solver.set_stream(stream.cuda_stream)
+        s.init_inidat()
+        enqueue, sync = s.enqueue, s.sync
+        rows_own = s.rows
+    else:
+        solver = api.HeatSolver(nx, ny, device=local_rank, **params)
+        solver.set_stream(stream.cuda_stream)
+        solver.init_inidat()
+        enqueue, sync = solver.enqueue, solver.sync
+        rows_own = nx
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    K, W = args.steps, max(args.warmup, 3)
+    if wl["conv_every"] > 0:
+        # the convergence-check loop is host-driven every conv_every updates: time heat_run itself
+        def enqueue(n):  # noqa: F811
+            solver.run(n)
+    enqueue(W)
+    sync()
+    barrier()
+    launches0 = solver.launch_count()
+    clocks = ClockSampler(local_rank)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    clocks.start()
+    e0.record(stream)
+    enqueue(K)
+    e1.record(stream)
+    sync()
+    barrier()
+    clk = clocks.stop()
+    ms = e0.elapsed_time(e1)
+    launches = solver.launch_count() - launches0
+    if world > 1:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    lups_per_update = (nx - 2) * (ny - 2)
+    value = lups_per_update * K / (ms * 1e-3) / 1e9
+
+    # roofline of the dominant kernel (the update kernel): this rank's algorithmic bytes per launch
+    peak, peak_src = measured_peak()
+    step_launches = K // wl["temporal_block"] if wl["temporal_block"] > 1 else K
+    own_lups = (min(rows_own, nx - 2) if world > 1 else nx - 2) * (ny - 2) * wl["temporal_block"]
+    kernel_ms = ms / max(step_launches, 1)
+    achieved = BYTES_PER_LUP * own_lups / (kernel_ms * 1e-3) / 1e9
+    kname = "heat_step_vec"
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": ncu_traffic(kname), "kernel": kname, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": BYTES_PER_LUP * own_lups,
+                "note": "8 B per point-update x interior points of this GPU's strip / mean launch time over the timed region"
+                        + (" (effective: temporal blocking re-uses tiles on chip)" if wl["temporal_block"] > 1 else "")}
+
+    # end to end: heat_solve() on HOST memory (pinned), H2D + K updates + D2H inside the timed region
+    e2e = None
+    if world == 1 and not args.no_e2e:
+        host = torch.empty((nx, ny), dtype=torch.float32, pin_memory=True)
+        hn = host.numpy()
+        hn[...] = api.inidat(nx, ny)
+        p = api.default_params(nx=nx, ny=ny, steps=K, device=local_rank, **params)
+        import ctypes as C
+        done, conv = C.c_int(0), C.c_int(0)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        rc = api.load().heat_solve(C.byref(p), hn.ctypes.data_as(C.POINTER(C.c_float)), C.byref(done), C.byref(conv))
+        dt = time.perf_counter() - t0
+        if rc != 0:
+            raise RuntimeError(api.load().heat_last_error().decode())
+        e2e = {"value": lups_per_update * done.value / dt / 1e9, "unit": "GLUP/s",
+               "h2d_bytes_per_step": nx * ny * 4 / max(done.value, 1), "d2h_bytes_per_step": nx * ny * 4 / max(done.value, 1),
+               "call": f"heat_solve(steps={K}) on pinned host memory: cudaMalloc + H2D of the {nx * ny * 4 >> 20} MiB field "
+                       f"+ {done.value} updates + D2H, wall clock", "seconds": dt}
+        launches_e2e = done.value
+    elif world > 1 and not args.no_e2e:
+        # strips: host field -> upload -> K updates -> gather on rank 0, wall clock, max over ranks
+        host = api.inidat(nx, ny) if args.e2e_multi else None
+        if host is not None:
+            barrier()
+            t0 = time.perf_counter()
+            s.upload(host)
+            s.enqueue(K)
+            s.sync()
+            s.gather(0)
+            barrier()
+            dt = time.perf_counter() - t0
+            e2e = {"value": lups_per_update * K / dt / 1e9, "unit": "GLUP/s",
+                   "h2d_bytes_per_step": nx * ny * 4 / K, "d2h_bytes_per_step": nx * ny * 4 / K,
+                   "call": "StripSolver.upload + enqueue + gather, wall clock", "seconds": dt}
+
+    base = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        base = cpu_baseline(wl)
+
+    if rank == 0:
+        out = {"metric": METRIC, "value": value, "unit": "GLUP/s", "n_gpus": world, "steps": K, "warmup": W,
+               "ms_per_step": ms / K, "higher_is_better": True, "scaling": wl["scaling"], "vs_baseline": None,
+               "dtype": "f32" if arith != api.MPI_F64MIX else "f32 grid, f64-mixed arithmetic",
+               "data": "synthetic",
+               "config": {"workload": wl["text"], "nx": nx, "ny": ny, "arith": api.ARITH_NAMES[arith],
+                          "conv_every": wl["conv_every"], "temporal_block": wl["temporal_block"],
+                          "halo": (args.halo if world > 1 else "none"),
+                          "l2": f"working set {2 * nx * ny * 4 >> 20} MiB vs 126 MB L2: inputs larger than L2, no flush "
+                                "(consecutive updates ARE the workload)"},
+               "roofline": roofline, "cpu_baseline": base, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk}
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        s.close()
+    else:
+        solver.close()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10000)
+    ap.add_argument("--warmup", type=int, default=50)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--workload", default="c2")
+    ap.add_argument("--arith", choices=["fma", "nofma", "f64mix"], default="fma")
+    ap.add_argument("--halo", choices=["p2p", "sendrecv"], default="p2p")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-multi", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    wl = workload(args.workload, max(world, 1) if args.impl == "ours" else max(args.gpus, 1))
+
+    if args.impl == "reference":
+        run_reference_arm(args, wl, rank, world)
+        return 0
+
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        run_ours(args, wl, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,173 @@
+/*
+ * heat_main.c -- drop-in program around libheat_b200.so (plain C, no CUDA in this file).
+ *
+ * It keeps the reference programs' surface so existing scripts and diffs keep working:
+ *   - the same compile-time macros as defaults: NXPROB NYPROB STEPS STEP CONVERGE
+ *     (mpi/mpi_heat_improved_persistent_stat.c:7-21, mpi/Makefile:12-22; cuda/cuda_heat.cu:7-16)
+ *   - the same stdout lines and .dat files (M:90-98,299-306; C:245-260)
+ *   - inidat()/prtdat() with the reference's names and arguments (M:315-341)
+ * and adds run-time options so one binary covers every size:
+ *   heat [--style mpi|cuda] [--nx N] [--ny N] [--steps S] [--step K] [--converge]
+ *        [--arith fma|nofma|f64mix] [--gpus G] [--no-dump] [--bin-dump]
+ * --style mpi  : STEPS+1 updates, check when (it+1)%STEP==0, MPI_F64MIX arithmetic,
+ *                initial_im.dat / final_im.dat, timer around setup+loop like M:88,298
+ * --style cuda : STEPS updates, check when it%20==0, F32_FMA arithmetic,
+ *                out_cuda_<1024>_<blocks>_<STEPS>.dat, timer around the loop only (C:203,239)
+ * The solver loop itself -- everything between the two timers -- runs on the GPU(s).
+ */
+#define _POSIX_C_SOURCE 200809L
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+
+#include "../include/heat.h"
+
+#ifndef NXPROB
+#define NXPROB 20
+#endif
+#ifndef NYPROB
+#define NYPROB 20
+#endif
+#ifndef STEPS
+#define STEPS 100
+#endif
+#ifndef STEP
+#define STEP 20 /* mpi/Makefile:8; cuda CHECK_INTERVAL C:16 */
+#endif
+#ifdef CONVERGE
+#define CONVERGE_DEFAULT 1
+#else
+#define CONVERGE_DEFAULT 0
+#endif
+#ifndef HEAT_STYLE
+#define HEAT_STYLE "mpi"
+#endif
+#define MAX_GPUS 16
+
+void inidat(int nx, int ny, float *u) { heat_inidat(nx, ny, u); }
+void prtdat(int nx, int ny, float *u, char *fnam) { heat_prtdat(nx, ny, u, fnam); }
+
+static double now(void)
+{
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec + 1e-9 * ts.tv_nsec;
+}
+
+static int die(const char *what)
+{
+    fprintf(stderr, "heat: %s: %s\n", what, heat_last_error());
+    return 1;
+}
+
+int main(int argc, char *argv[])
+{
+    int nx = NXPROB, ny = NYPROB, steps = STEPS, step = STEP, converge = CONVERGE_DEFAULT;
+    int gpus = 1, dump = 1, bin_dump = 0, arith = -1;
+    const char *style = HEAT_STYLE;
+    for (int i = 1; i < argc; i++) {
+        const char *a = argv[i];
+        const char *v = (i + 1 < argc) ? argv[i + 1] : NULL;
+        if (!strcmp(a, "--nx") && v) nx = atoi(argv[++i]);
+        else if (!strcmp(a, "--ny") && v) ny = atoi(argv[++i]);
+        else if (!strcmp(a, "--size") && v) nx = ny = atoi(argv[++i]);
+        else if (!strcmp(a, "--steps") && v) steps = atoi(argv[++i]);
+        else if (!strcmp(a, "--step") && v) step = atoi(argv[++i]);
+        else if (!strcmp(a, "--gpus") && v) gpus = atoi(argv[++i]);
+        else if (!strcmp(a, "--style") && v) style = argv[++i];
+        else if (!strcmp(a, "--converge")) converge = 1;
+        else if (!strcmp(a, "--no-dump")) dump = 0;
+        else if (!strcmp(a, "--bin-dump")) bin_dump = 1;
+        else if (!strcmp(a, "--arith") && v) {
+            const char *m = argv[++i];
+            arith = !strcmp(m, "fma") ? HEAT_F32_FMA : !strcmp(m, "nofma") ? HEAT_F32_NOFMA : !strcmp(m, "f64mix") ? HEAT_MPI_F64MIX : -2;
+        } else {
+            fprintf(stderr, "usage: %s [--style mpi|cuda] [--nx N] [--ny N] [--size N] [--steps S] [--step K] [--converge]\n"
+                            "       [--arith fma|nofma|f64mix] [--gpus G] [--no-dump] [--bin-dump]\n", argv[0]);
+            return 2;
+        }
+    }
+    const int mpi_style = strcmp(style, "cuda") != 0;
+    if (arith == -2 || gpus < 1 || gpus > MAX_GPUS) {
+        fprintf(stderr, "heat: bad --arith or --gpus\n");
+        return 2;
+    }
+
+    heat_params p;
+    heat_params_default(&p);
+    p.nx = nx;
+    p.ny = ny;
+    p.steps = steps;
+    p.conv_every = converge ? step : 0;
+    p.step_convention = mpi_style ? HEAT_STEPS_MPI : HEAT_STEPS_CUDA;
+    p.conv_phase = mpi_style ? HEAT_PHASE_MPI : HEAT_PHASE_CUDA;
+    p.arith = arith >= 0 ? arith : (mpi_style ? HEAT_MPI_F64MIX : HEAT_F32_FMA);
+    p.nranks = gpus;
+
+    float *grid = (float *)malloc((size_t)nx * ny * sizeof(float));
+    if (!grid) {
+        perror("malloc for grid");
+        return -1;
+    }
+
+    const double starttime = now(); /* M:88: the MPI program's timer starts before inidat */
+    if (mpi_style) {
+        printf("Starting mpi_heat2D with %d worker tasks.\n", gpus);
+        if (!converge) printf("Grid size: X= %d  Y= %d  Time steps= %d\n", nx, ny, steps);
+        else printf("Grid size: X= %d  Y= %d  Time steps= - \n", nx, ny);
+    }
+    inidat(nx, ny, grid);
+    if (mpi_style && dump) prtdat(nx, ny, grid, "initial_im.dat");
+
+    /* one strip per GPU, all driven by this host thread */
+    heat_handle *h[MAX_GPUS] = {0};
+    for (int r = 0; r < gpus; r++) {
+        p.rank = r;
+        p.device = r;
+        if (heat_create(&p, &h[r])) return die("heat_create");
+    }
+    for (int r = 0; r < gpus && gpus > 1; r++)
+        if (heat_connect_local(h[r], r > 0 ? h[r - 1] : NULL, r < gpus - 1 ? h[r + 1] : NULL)) return die("heat_connect_local");
+    for (int r = 0; r < gpus; r++)
+        if (heat_upload(h[r], grid)) return die("heat_upload");
+
+    int done = 0, conv = 0;
+    if (heat_group_run(h, gpus, steps, &done, &conv)) return die("heat_run");
+    float loop_ms = 0.0f;
+    heat_elapsed_ms(h[0], &loop_ms);
+
+    for (int r = 0; r < gpus; r++)
+        if (heat_download(h[r], grid)) return die("heat_download");
+    const double endtime = now(); /* M:298: stops before the final dump */
+
+    if (mpi_style) {
+        if (dump) prtdat(nx, ny, grid, "final_im.dat");
+        if (bin_dump) heat_prtdat_bin(nx, ny, grid, "final_im.bin");
+        if (converge) {
+            if (conv) printf("Converged after %d steps\n", done - 1); /* M:302 prints the 0-based it */
+            else printf("Didn't converged\n");
+        }
+        printf("Elapsed time %f secs\n", endtime - starttime);
+    } else {
+        /* C:17-21,246-251: THREADS_PER_BLOCK 1024 and the 32x32-block count appear in the file name */
+        char buf[256];
+        const int rb = (nx - 2) / 32 + ((nx - 2) % 32 ? 1 : 0), cb = (ny - 2) / 32 + ((ny - 2) % 32 ? 1 : 0);
+        snprintf(buf, sizeof buf, "out_cuda_%d_%d_%d.dat", 1024, rb * cb, steps);
+        if (dump) prtdat(nx, ny, grid, buf);
+        if (bin_dump) heat_prtdat_bin(nx, ny, grid, "out_cuda.bin");
+        if (converge) {
+            if (conv) printf("Converged at %d steps\n", done - 1); /* C:256 prints the 0-based i */
+            else printf("Did not converge\n");
+        }
+        const float msecs = loop_ms; /* C:203,239: the loop only (here with the device synchronised) */
+        printf("Elapsed time: %.3f %ssecs\n", (msecs / 1000 > 1.0 ? msecs / 1000 : msecs), (msecs / 1000 > 1.0 ? "" : "m"));
+    }
+    /* one machine-readable line on stderr; stdout stays the reference's */
+    fprintf(stderr, "{\"nx\": %d, \"ny\": %d, \"updates\": %d, \"converged\": %d, \"loop_ms\": %.3f, \"glups\": %.3f, \"gpus\": %d, \"arith\": %d}\n",
+            nx, ny, done, conv, loop_ms, loop_ms > 0 ? (double)(nx - 2) * (ny - 2) * done / (loop_ms * 1e6) : 0.0, gpus, p.arith);
+
+    for (int r = 0; r < gpus; r++) heat_destroy(h[r]);
+    free(grid);
+    return 0;
+}

@@ -1,0 +1,114 @@
+"""CPU-side checks of the C ABI: the library builds for sm_100a, loads, exports every symbol
+include/heat.h declares, its host helpers match the reference, and -- without a GPU -- every
+compute entry point fails loudly instead of falling back to a CPU path."""
+import ctypes as C
+import hashlib
+import re
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def declared_symbols():
+    text = (ROOT / "include" / "heat.h").read_text()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(heat_[a-z0-9_]+)\s*\(", text)) - {"heat_allreduce_max_fn"})
+
+
+def test_library_exports_every_declared_symbol(ph):
+    lib = C.CDLL(str(ph.api.LIB_PATH))
+    names = declared_symbols()
+    assert len(names) >= 30
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/heat.h but not exported"
+    # and the ctypes mirror binds exactly that set
+    assert sorted(ph.api.SIGNATURES) == names
+
+
+def test_params_default_is_the_reference_default(ph):
+    p = ph.default_params()
+    assert (p.nx, p.ny, p.steps) == (20, 20, 100)  # M:7-18
+    assert p.cx == np.float32(0.1) and p.cy == np.float32(0.1)  # struct Parms, M:29-32
+    assert p.conv_every == 0 and p.conv_eps == np.float32(1e-3)
+    assert p.nranks == 1 and p.temporal_block == 1
+    assert C.sizeof(ph.HeatParams) == 14 * 4
+
+
+def test_host_inidat_and_prtdat_match_reference(ph, golden, tmp_path):
+    e = [x for x in golden["plain"] if x["nx"] == 20 and x["steps"] == 100][0]
+    u = ph.inidat(20, 20)
+    assert hashlib.sha256(u.tobytes()).hexdigest() == e["initial_sha256"]
+    ph.prtdat(u, tmp_path / "initial_im.dat")
+    assert hashlib.md5((tmp_path / "initial_im.dat").read_bytes()).hexdigest() == e["initial_text_md5"]
+    big = ph.inidat(1024, 1024)
+    e = [x for x in golden["plain"] if x["nx"] == 1024][0]
+    assert hashlib.sha256(big.tobytes()).hexdigest() == e["initial_sha256"]
+    for n, want in golden["inidat_centre"].items():
+        if int(n) <= 8192:
+            assert float(ph.inidat(int(n), int(n))[int(n) // 2, int(n) // 2]) == want
+
+
+def test_binary_dump_round_trip(ph, tmp_path):
+    u = ph.inidat(33, 47)
+    ph.prtdat_bin(u, tmp_path / "u.bin")
+    assert (tmp_path / "u.bin").stat().st_size == 16 + u.nbytes
+    assert np.array_equal(ph.readdat_bin(tmp_path / "u.bin").view(np.uint32), u.view(np.uint32))
+    (tmp_path / "bad.bin").write_bytes(b"not a dump")
+    with pytest.raises(ph.HeatError):
+        ph.readdat_bin(tmp_path / "bad.bin")
+
+
+def test_strip_rows_partition(ph):
+    for nx, g in [(10, 3), (65536, 8), (16384, 4), (7, 7), (1026, 5)]:
+        parts = [ph.strip_rows(nx, g, r) for r in range(g)]
+        assert parts[0][0] == 0 and sum(n for _, n in parts) == nx
+        for (a, n), (b, _) in zip(parts, parts[1:]):
+            assert a + n == b
+        assert max(n for _, n in parts) - min(n for _, n in parts) <= 1
+    with pytest.raises(ph.HeatError):
+        ph.strip_rows(4, 5, 0)
+    with pytest.raises(ph.HeatError):
+        ph.strip_rows(10, 2, 2)
+
+
+def test_bad_arguments_are_rejected_with_a_message(ph):
+    lib = ph.load()
+    assert lib.heat_inidat(0, 5, None) == ph.api.E_INVALID
+    assert b"heat_inidat" in lib.heat_last_error()
+    assert lib.heat_solve(None, None, None, None) == ph.api.E_INVALID
+    p = ph.default_params(nx=0)
+    g = np.zeros((4, 4), np.float32)
+    assert lib.heat_solve(C.byref(p), g.ctypes.data_as(C.POINTER(C.c_float)), None, None) == ph.api.E_INVALID
+    for bad in (dict(arith=7), dict(temporal_block=3), dict(rank=2, nranks=2), dict(steps=-1), dict(conv_every=-2)):
+        h = C.c_void_p()
+        p = ph.default_params(**bad)
+        assert lib.heat_create(C.byref(p), C.byref(h)) == ph.api.E_INVALID, bad
+        assert not h.value
+
+
+@pytest.mark.skipif(__import__("torch").cuda.is_available(), reason="only meaningful on a box without a GPU")
+def test_no_cpu_fallback_without_a_gpu(ph):
+    assert ph.device_count() == 0
+    with pytest.raises(ph.HeatError) as ei:
+        ph.solve(ph.inidat(20, 20), 5)
+    assert ei.value.code == ph.api.E_CUDA
+    with pytest.raises(ph.HeatError):
+        ph.HeatSolver(20, 20)
+
+
+def test_missing_library_fails_loudly(ph, monkeypatch, tmp_path):
+    monkeypatch.setattr(ph.api, "_lib", None)
+    monkeypatch.setattr(ph.api, "LIB_PATH", tmp_path / "nope.so")
+    with pytest.raises(ph.HeatError, match="no CPU fallback"):
+        ph.api.load()
+
+
+def test_product_never_imports_the_oracle():
+    # parity claims are void if the shipped path can reach oracle/ (tier rule 3)
+    for f in list((ROOT / "parallel_heat_b200").rglob("*.py")) + list((ROOT / "parallel_heat_b200").rglob("*.cu*")) \
+            + list((ROOT / "src").rglob("*.c")) + [ROOT / "include" / "heat.h"]:
+        text = f.read_text()
+        assert "pyoracle" not in text and "heat_oracle" not in text and "oracle/" not in text.replace("oracle/_ref", ""), f

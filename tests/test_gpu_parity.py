@@ -1,0 +1,302 @@
+"""GPU parity tests: libheat_b200.so (through its C ABI) against the CPU oracle, the golden
+vectors of the reference MPI program, and size-independent properties at full size.
+Everything here is bit-exact: each arithmetic mode reproduces one build of the reference."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+MODES = [0, 1, 2]  # F32_FMA, F32_NOFMA, MPI_F64MIX (same numbering in the oracle)
+
+
+def bits(a):
+    return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a, np.float32).tobytes()).hexdigest()
+
+
+def assert_same_bits(a, b, what=""):
+    a, b = bits(a), bits(b)
+    if not np.array_equal(a, b):
+        bad = np.argwhere(a != b)
+        fa, fb = a.view(np.float32), b.view(np.float32)
+        raise AssertionError(f"{what}: {len(bad)} of {a.size} values differ, first at {tuple(bad[0])}: "
+                             f"{fa[tuple(bad[0])]!r} vs {fb[tuple(bad[0])]!r}")
+
+
+def field(shape, seed=0, scale=1e3):
+    return (np.random.default_rng(seed).standard_normal(shape) * scale).astype(np.float32)
+
+
+# ---------------------------------------------------------------- K0 inidat
+@pytest.mark.parametrize("shape", [(20, 20), (431, 431), (432, 432), (33, 47), (1024, 1024), (1000, 1026), (3, 5)])
+def test_device_inidat_is_the_host_inidat(ph, oracle, shape):
+    with ph.HeatSolver(*shape) as s:
+        s.init_inidat()
+        assert_same_bits(s.download(), oracle.inidat(*shape), f"inidat {shape}")
+
+
+def test_device_inidat_8192_wraps_like_the_reference(ph, golden):
+    with ph.HeatSolver(8192, 8192) as s:
+        s.init_inidat()
+        u = s.download()
+    assert float(u[4096, 4096]) == golden["inidat_centre"]["8192"]
+    rows = [0, 1, 431, 432, 4095, 8190, 8191]
+    host = ph.inidat(8192, 8192)
+    assert_same_bits(u[rows], host[rows], "inidat 8192 sampled rows")
+
+
+# ---------------------------------------------------------------- K1: updates vs oracle
+SHAPES = [(3, 3), (3, 9), (9, 3), (4, 4), (5, 5), (20, 20), (33, 47), (47, 33), (64, 4), (4, 64), (129, 257),
+          (130, 1000), (1000, 1026), (1026, 1000), (257, 4100)]
+
+
+@pytest.mark.parametrize("arith", MODES)
+@pytest.mark.parametrize("shape", SHAPES)
+def test_updates_bit_exact_vs_oracle(ph, oracle, shape, arith):
+    u = field(shape, seed=shape[0] * 7 + shape[1])
+    for steps in (1, 2, 7):
+        want, _, _ = oracle.solve(u, steps, arith=arith)
+        got, done, conv = ph.solve(u, steps, arith=arith)
+        assert done == steps and not conv
+        assert_same_bits(got, want, f"{shape} arith={arith} steps={steps}")
+
+
+@pytest.mark.parametrize("arith", MODES)
+def test_ring_and_both_buffers(ph, oracle, arith):
+    # a NON-zero ring: the solver may not assume inidat's zero boundary
+    u = field((37, 53), seed=5)
+    with ph.HeatSolver(37, 53, arith=arith) as s:
+        s.upload(u)
+        s.run(3)
+        newest = s.download()
+        for sl in (np.s_[0], np.s_[-1], np.s_[:, 0], np.s_[:, -1]):
+            assert_same_bits(newest[sl], u[sl], "ring")
+        want3, _, _ = oracle.solve(u, 3, arith=arith)
+        assert_same_bits(newest, want3)
+        s.run(1)  # the other buffer now holds update 4; its ring must be intact too
+        want4, _, _ = oracle.solve(u, 4, arith=arith)
+        assert_same_bits(s.download(), want4)
+
+
+@pytest.mark.parametrize("shape", [(1, 1), (1, 9), (2, 2), (2, 50), (50, 2), (2, 3)])
+def test_no_interior_means_no_change(ph, shape):
+    u = field(shape, seed=1)
+    got, done, _ = ph.solve(u, 5)
+    assert done == 5
+    assert_same_bits(got, u)
+
+
+def test_step_conventions(ph, oracle):
+    u = ph.inidat(20, 20)
+    got, done, _ = ph.solve(u, 0)
+    assert done == 0 and np.array_equal(got, u)
+    got, done, _ = ph.solve(u, 0, step_convention=ph.STEPS_MPI)  # M:159 `it <= STEPS`
+    assert done == 1
+    assert_same_bits(got, oracle.solve(u, 1)[0])
+
+
+@pytest.mark.parametrize("rpt", [1, 3, 7, 64, 1000])
+def test_tiling_does_not_change_bits(ph, oracle, rpt, monkeypatch):
+    monkeypatch.setenv("HEAT_ROWS_PER_TILE", str(rpt))
+    u = field((131, 520), seed=9)
+    for arith in MODES:
+        got, _, _ = ph.solve(u, 5, arith=arith)
+        assert_same_bits(got, oracle.solve(u, 5, arith=arith)[0], f"rows_per_tile={rpt}")
+
+
+def test_serpentine_sweep_does_not_change_bits(ph, monkeypatch):
+    u = ph.inidat(300, 300)
+    a, _, _ = ph.solve(u, 9)
+    monkeypatch.setenv("HEAT_SERPENTINE", "0")
+    b, _, _ = ph.solve(u, 9)
+    assert_same_bits(a, b)
+
+
+# ---------------------------------------------------------------- golden vectors of the reference
+def test_golden_reference_mpi_outputs(ph, golden):
+    for e in golden["plain"]:
+        got, done, conv = ph.solve(ph.inidat(e["nx"], e["ny"]), e["steps"], arith=ph.MPI_F64MIX,
+                                   step_convention=ph.STEPS_MPI)
+        assert done == e["updates"] and not conv
+        assert sha(got) == e["final_sha256"], e
+        key = f"final_{e['nx']}x{e['ny']}_s{e['steps']}"
+        if key in golden["arrays"]:
+            assert np.array_equal(bits(got), golden["arrays"][key])
+
+
+def test_golden_text_dump_md5(ph, golden, tmp_path):
+    # BASELINE config 1 end to end: 1024 x 1024, STEPS=1000, final_im.dat md5 of the reference
+    e = [x for x in golden["plain"] if x["nx"] == 1024 and x["steps"] == 1000][0]
+    got, _, _ = ph.solve(ph.inidat(1024, 1024), 1000, arith=ph.MPI_F64MIX, step_convention=ph.STEPS_MPI)
+    ph.prtdat(got, tmp_path / "final_im.dat")
+    assert hashlib.md5((tmp_path / "final_im.dat").read_bytes()).hexdigest() == e["final_text_md5"]
+
+
+def test_float_modes_within_tolerance_of_the_mpi_reference(ph, golden):
+    # north_star: <= 1e-5 relative (max-abs / max|u|) between the float builds and the MPI build
+    ini = ph.inidat(1024, 1024)
+    ref, _, _ = ph.solve(ini, 1000, arith=ph.MPI_F64MIX, step_convention=ph.STEPS_MPI)
+    scale = np.abs(ref).max()
+    for arith in (ph.F32_FMA, ph.F32_NOFMA):
+        got, _, _ = ph.solve(ini, 1000, arith=arith, step_convention=ph.STEPS_MPI)
+        assert np.abs(got - ref).max() / scale <= 1e-5
+
+
+# ---------------------------------------------------------------- K2: convergence
+def test_convergence_matches_the_reference_print(ph, golden):
+    for e in golden["conv"]:
+        got, done, conv = ph.solve(ph.inidat(e["nx"], e["ny"]), e["steps"], arith=ph.MPI_F64MIX,
+                                   step_convention=ph.STEPS_MPI, conv_every=e["step"], conv_phase=ph.PHASE_MPI)
+        if e["printed"] is None:
+            assert not conv and done == e["steps"] + 1
+        else:
+            assert conv and done - 1 == e["printed"], e
+        assert sha(got) == e["final_sha256"]
+
+
+@pytest.mark.parametrize("arith", MODES)
+@pytest.mark.parametrize("phase", [0, 1])
+def test_convergence_vs_oracle(ph, oracle, arith, phase):
+    for shape, K in [((20, 20), 20), ((20, 20), 7), ((33, 47), 5), ((64, 200), 20)]:
+        u = ph.inidat(*shape)
+        want, wdone, wconv = oracle.solve(u, 10000, arith=arith, conv_every=K, conv_phase=phase)
+        got, done, conv = ph.solve(u, 10000, arith=arith, conv_every=K, conv_phase=phase)
+        assert (done, conv) == (wdone, wconv)
+        assert conv or shape == (64, 200)  # the small grids settle well inside 10000 updates
+        assert_same_bits(got, want)
+
+
+def test_fused_residual_equals_separate_pass(ph, oracle):
+    u = field((200, 328), seed=11)
+    with ph.HeatSolver(200, 328, conv_every=1, conv_eps=0.0) as s:  # eps 0: checks every update, never stops
+        s.upload(u)
+        done, conv = s.run(4)
+        assert done == 4 and not conv
+        sep = s.residual()
+    a, _, _ = oracle.solve(u, 3)
+    b, _, _ = oracle.solve(u, 4)
+    assert sep == oracle.max_abs_diff(a, b)
+
+
+def test_run_can_be_resumed(ph, oracle):
+    u = ph.inidat(64, 64)
+    with ph.HeatSolver(64, 64, conv_every=20, conv_phase=ph.PHASE_MPI, arith=ph.MPI_F64MIX) as s:
+        s.upload(u)
+        total = 0
+        for chunk in (7, 13, 50, 1000, 100000):
+            d, conv = s.run(chunk)
+            total += d
+            if conv:
+                break
+        got = s.download()
+    want, wdone, wconv = oracle.solve(u, 200000, arith=2, conv_every=20, conv_phase=0)
+    assert conv and wconv and total == wdone
+    assert_same_bits(got, want)
+
+
+# ---------------------------------------------------------------- stateless entry points
+@pytest.mark.parametrize("arith", MODES)
+def test_stateless_step_device(ph, oracle, arith):
+    import torch
+    for shape in [(20, 20), (33, 47), (257, 130)]:
+        u = field(shape, seed=2)
+        d_in = torch.from_numpy(u).cuda()
+        d_out = torch.full(shape, -7.0, device="cuda")  # ring of d_out must stay -7
+        resid = torch.zeros(1, dtype=torch.int32, device="cuda")
+        ph.step_residual_device(d_in.data_ptr(), d_out.data_ptr(), shape[0], shape[1], resid.data_ptr(), arith=arith,
+                                stream=torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        out = d_out.cpu().numpy()
+        want = oracle.step(u, arith, out=np.full(shape, -7.0, np.float32))
+        assert_same_bits(out, want, f"stateless {shape}")
+        r = resid.cpu().numpy().view(np.float32)[0]
+        assert r == np.abs(u[1:-1, 1:-1] - want[1:-1, 1:-1]).max()
+        d_out2 = torch.full(shape, -7.0, device="cuda")
+        ph.step_device(d_in.data_ptr(), d_out2.data_ptr(), shape[0], shape[1], arith=arith)
+        torch.cuda.synchronize()
+        assert_same_bits(d_out2.cpu().numpy(), want)
+
+
+# ---------------------------------------------------------------- strips (one GPU, several strips)
+def run_strips(ph, u, g, steps, **params):
+    nx, ny = u.shape
+    ss = [ph.HeatSolver(nx, ny, rank=r, nranks=g, **params) for r in range(g)]
+    try:
+        for r, s in enumerate(ss):
+            s.connect_local(ss[r - 1] if r > 0 else None, ss[r + 1] if r < g - 1 else None)
+        for s in ss:
+            s.upload(u)
+        done, conv = ph.group_run(ss, steps)
+        out = np.zeros_like(u)
+        for s in ss:
+            s.download(out)
+        return out, done, conv
+    finally:
+        for s in ss:
+            s.close()
+
+
+@pytest.mark.parametrize("g", [2, 3, 4, 8])
+@pytest.mark.parametrize("arith", MODES)
+def test_strip_decomposition_is_bit_identical(ph, oracle, g, arith):
+    for shape in [(64, 64), (67, 130), (258, 36)]:
+        if shape[0] // g < 2:
+            continue
+        u = field(shape, seed=g)
+        want, _, _ = oracle.solve(u, 25, arith=arith)
+        got, done, _ = run_strips(ph, u, g, 25, arith=arith)
+        assert done == 25
+        assert_same_bits(got, want, f"{g} strips {shape}")
+
+
+def test_strips_convergence(ph, oracle):
+    u = ph.inidat(40, 24)
+    want, wdone, wconv = oracle.solve(u, 100000, arith=2, conv_every=20, conv_phase=0, step_convention=1)
+    got, done, conv = run_strips(ph, u, 4, 100000, arith=2, conv_every=20, conv_phase=0, step_convention=1)
+    assert wconv and conv and done == wdone
+    assert_same_bits(got, want)
+
+
+def test_unconnected_strip_refuses_to_run(ph):
+    with ph.HeatSolver(64, 64, rank=0, nranks=2) as s:
+        with pytest.raises(ph.HeatError) as ei:
+            s.upload(ph.inidat(64, 64))
+        assert ei.value.code == ph.api.E_STATE
+
+
+# ---------------------------------------------------------------- full-size checks
+def test_8192_bit_exact_vs_oracle_and_properties(ph, oracle):
+    # BASELINE config 2's grid; the oracle does a few updates of it in seconds
+    n, steps = 8192, 6
+    ini = ph.inidat(n, n)
+    with ph.HeatSolver(n, n, arith=ph.F32_FMA) as s:
+        s.init_inidat()
+        s.run(steps)
+        got = s.download()
+    want, _, _ = oracle.solve(ini, steps, arith=0)
+    assert_same_bits(got, want, "8192^2")
+    assert got.max() <= ini.max() and got.min() >= ini.min()  # max principle
+    for sl in (np.s_[0], np.s_[-1], np.s_[:, 0], np.s_[:, -1]):
+        assert not got[sl].any()
+    # decomposition independence at full size: 4 strips give the same bits
+    parts, _, _ = run_strips(ph, ini, 4, steps, arith=ph.F32_FMA)
+    assert_same_bits(parts, want, "8192^2 in 4 strips")
+
+
+def test_16384_with_convergence_check(ph, oracle):
+    # BASELINE config 3's grid: check every 20 updates (never converges on the wrapped field)
+    n = 16384
+    with ph.HeatSolver(n, n, arith=ph.F32_FMA, conv_every=20) as s:
+        s.init_inidat()
+        done, conv = s.run(41)
+        assert done == 41 and not conv
+        got = s.download()
+    want, wdone, wconv = oracle.solve(oracle.inidat(n, n), 41, arith=0, conv_every=20, conv_phase=1)
+    assert wdone == 41 and not wconv
+    assert_same_bits(got, want, "16384^2")
