@@ -128,6 +128,23 @@ int heat_step_device(const void *d_in, void *d_out, int nx, int ny, float cx, fl
 int heat_step_residual_device(const void *d_in, void *d_out, int nx, int ny, float cx, float cy, int arith,
                               void *d_residual_bits, void *stream);
 
+/* Same update + residual as heat_step_residual_device, for callers that cannot allocate: an
+ * application that gave all of the GPU's memory to its own pool, or a time loop that cannot
+ * afford the device-wide synchronisation of cudaMalloc/cudaFree.  It has no counterpart in the
+ * reference.  The reduction's working memory is a fixed array inside the library image
+ * (HEAT_NOALLOC_SCRATCH_BYTES, held by every GPU that loads the library until the process
+ * exits), so the call performs no allocation.  The caller passes the input field, the output
+ * field (dense nx*ny, ring left untouched) and d_residual, one device float that receives
+ * max|old-new|; nothing needs zeroing beforehand.  Limits and rules: ny <= HEAT_NOALLOC_MAX_NY,
+ * larger rows are refused with HEAT_E_INVALID; all calls on one GPU share the array, so calls
+ * that overlap on that GPU race -- issue them one after another; the first call on a GPU
+ * looks up the array's address and should be made outside any stream capture. */
+#define HEAT_NOALLOC_MAX_BLOCKS    16384
+#define HEAT_NOALLOC_SCRATCH_BYTES ((HEAT_NOALLOC_MAX_BLOCKS + 64) * 4)
+#define HEAT_NOALLOC_MAX_NY        (HEAT_NOALLOC_MAX_BLOCKS * 256 + 2)
+int heat_step_residual_noalloc(const void *d_in, void *d_out, int nx, int ny, float cx, float cy, int arith,
+                               void *d_residual, void *stream);
+
 /* ---- row strips across GPUs (replaces the 2-D block topology + persistent halo requests,
  *      M:51-84,130-155,160-161,177,263) --------------------------------------------------
  * Strip r of n owns global rows [row0, row0+rows).  Each strip keeps one ghost row per

@@ -73,6 +73,8 @@ SIGNATURES = {
     "heat_step_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, C.c_void_p]),
     "heat_step_residual_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int,
                                             C.c_void_p, C.c_void_p]),
+    "heat_step_residual_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int,
+                                             C.c_void_p, C.c_void_p]),
     "heat_strip_rows": (C.c_int, [C.c_int, C.c_int, C.c_int, _ip, _ip]),
     "heat_set_halo_mode": (C.c_int, [_H, C.c_int]),
     "heat_ipc_export": (C.c_int, [_H, C.c_void_p, C.c_size_t]),
@@ -297,3 +299,15 @@ def step_device(d_in, d_out, nx, ny, cx=0.1, cy=0.1, arith=F32_FMA, stream=0):
 def step_residual_device(d_in, d_out, nx, ny, d_residual_bits, cx=0.1, cy=0.1, arith=F32_FMA, stream=0):
     _check(load().heat_step_residual_device(C.c_void_p(d_in), C.c_void_p(d_out), nx, ny, cx, cy, arith,
                                             C.c_void_p(d_residual_bits), C.c_void_p(stream)))
+
+
+NOALLOC_MAX_NY = 16384 * 256 + 2
+
+
+def step_residual_noalloc(d_in, d_out, nx, ny, d_residual, cx=0.1, cy=0.1, arith=F32_FMA, stream=0):
+    """heat_step_residual_noalloc(): the update + residual for callers that cannot allocate (their
+    own pool owns the GPU's memory, or cudaMalloc's device-wide sync is unaffordable).  d_residual
+    is one device float; the reduction works in a fixed array inside the library, shared by all
+    calls on a GPU (do not overlap them); ny is limited to NOALLOC_MAX_NY."""
+    _check(load().heat_step_residual_noalloc(C.c_void_p(d_in), C.c_void_p(d_out), nx, ny, cx, cy, arith,
+                                             C.c_void_p(d_residual), C.c_void_p(stream)))

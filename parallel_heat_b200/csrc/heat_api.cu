@@ -5,6 +5,7 @@
 #include "heat_kernels.cuh"
 
 #include <cuda.h>
+#include <mutex>
 #include <new>
 #include <stdarg.h>
 #include <stdio.h>
@@ -792,5 +793,143 @@ extern "C" int heat_connect_local(heat_handle* h, heat_handle* north, heat_handl
         h->local_nb[side] = o;
     }
     h->connected = true;
+    return HEAT_OK;
+}
+
+// ------------------------------------------------------------------ update + residual without any allocation
+// heat_step_residual_noalloc() is for callers that must not allocate: a host application that
+// handed all of the GPU's memory to its own pool at start-up, or a solver loop with a hard
+// latency budget that cannot afford the device-wide synchronisation a cudaMalloc/cudaFree
+// implies.  Such a caller can still pass its input field, its output field and a 4-byte result
+// slot, but it has nowhere to get the reduction's working memory from.  Here that working
+// memory is a fixed array that is part of the library image, so the call allocates nothing.
+//
+// What to know before using it:
+//   * The array belongs to the GPU, not to the call.  Every GPU that loads this library keeps
+//     HEAT_NOALLOC_SCRATCH_BYTES of it until the process exits, and every call on that GPU uses
+//     the same one.  Two calls that overlap on one GPU (two streams, two host threads) would
+//     trample each other's partial results: run them one after another.
+//   * The first call on a given GPU looks up the array's device address and remembers it.
+//     Make that first call outside any stream capture.
+//   * The array keeps whatever the previous call left in it.  The one word that has to start
+//     at zero, the arrival counter, is cleared on the stream at the start of every call.
+//   * Row length is limited to HEAT_NOALLOC_MAX_NY (one slot per thread block,
+//     HEAT_NOALLOC_MAX_BLOCKS slots); longer rows are refused with HEAT_E_INVALID.
+namespace noalloc {
+
+constexpr int kThreads = 256;
+constexpr int kSlots = HEAT_NOALLOC_MAX_BLOCKS; // one partial maximum per thread block
+constexpr int kCounter = kSlots;                // the arrival counter sits behind the slots
+constexpr int kWords = kSlots + 64;
+static_assert(kWords * sizeof(unsigned) == HEAT_NOALLOC_SCRATCH_BYTES, "include/heat.h and the array disagree");
+static_assert((long long)kSlots * kThreads + 2 == HEAT_NOALLOC_MAX_NY, "include/heat.h and the launch shape disagree");
+
+// The working memory.  In host code this name is only a stand-in for the symbol, NOT a device
+// address; host code gets the real address once per device from cudaGetSymbolAddress() below.
+static __device__ __align__(256) unsigned scratch_words[kWords];
+
+constexpr int kMaxDevices = 64;
+static std::mutex lock;
+static unsigned* scratch_addr[kMaxDevices]; // device address of the array, by device ordinal
+
+// The update of heat_step_generic; each block leaves its maximum in its slot and the block
+// that arrives last folds the slots into *d_residual.
+template <int ARITH>
+__global__ void __launch_bounds__(kThreads)
+step_partials(const float* __restrict__ in, float* __restrict__ out, int nx, int ny, float cx, float cy, unsigned* scratch,
+              float* d_residual)
+{
+    const int j = blockIdx.x * kThreads + threadIdx.x + 1;
+    float m = 0.0f;
+    if (j < ny - 1) {
+        for (int i = blockIdx.y + 1; i < nx - 1; i += gridDim.y) {
+            const float* c = in + (int64_t)i * ny + j;
+            const float cv = c[0];
+            const float o = upd<ARITH>(cv, c[-ny], c[ny], c[1], c[-1], cx, cy);
+            out[(int64_t)i * ny + j] = o;
+            m = fmaxf(m, fabsf(__fsub_rn(cv, o)));
+        }
+    }
+    __shared__ unsigned warp_max[kThreads / 32];
+    __shared__ bool last_block;
+    const unsigned bits = __reduce_max_sync(0xffffffffu, __float_as_uint(m));
+    if ((threadIdx.x & 31) == 0) warp_max[threadIdx.x >> 5] = bits;
+    __syncthreads();
+    const unsigned nblocks = gridDim.x * gridDim.y;
+    if (threadIdx.x == 0) {
+        unsigned v = 0;
+        for (int w = 0; w < kThreads / 32; w++) v = max(v, warp_max[w]);
+        scratch[blockIdx.y * gridDim.x + blockIdx.x] = v;
+        __threadfence(); // the slot is visible before the ticket is taken
+        last_block = (atomicAdd(&scratch[kCounter], 1u) == nblocks - 1);
+    }
+    __syncthreads();
+    if (last_block) {
+        unsigned v = 0;
+        for (unsigned k = threadIdx.x; k < nblocks; k += kThreads) v = max(v, __ldcg(&scratch[k]));
+        v = __reduce_max_sync(0xffffffffu, v);
+        if ((threadIdx.x & 31) == 0) warp_max[threadIdx.x >> 5] = v;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned r = 0;
+            for (int w = 0; w < kThreads / 32; w++) r = max(r, warp_max[w]);
+            *d_residual = __uint_as_float(r);
+            scratch[kCounter] = 0; // leave the counter clean for the next call as well
+        }
+    }
+}
+
+// Device address of the array on the CURRENT device; looked up on first use.
+static int scratch_for_current_device(unsigned** out)
+{
+    int dev = -1;
+    CK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return fail(HEAT_E_INVALID, "heat_step_residual_noalloc: device ordinal %d not supported", dev);
+    std::lock_guard<std::mutex> guard(lock);
+    if (!scratch_addr[dev]) {
+        unsigned* ptr = nullptr;
+        CK(cudaGetSymbolAddress((void**)&ptr, scratch_words));
+        if (!ptr) return fail(HEAT_E_CUDA, "heat_step_residual_noalloc: cudaGetSymbolAddress returned no address");
+        scratch_addr[dev] = ptr;
+    }
+    *out = scratch_addr[dev];
+    return HEAT_OK;
+}
+
+} // namespace noalloc
+
+extern "C" int heat_step_residual_noalloc(const void* d_in, void* d_out, int nx, int ny, float cx, float cy, int arith,
+                                          void* d_residual, void* stream)
+{
+    using namespace noalloc;
+    if (!d_in || !d_out || !d_residual || nx < 1 || ny < 1 || arith < HEAT_F32_FMA || arith > HEAT_MPI_F64MIX)
+        return fail(HEAT_E_INVALID, "heat_step_residual_noalloc: bad arguments");
+    if (ny > HEAT_NOALLOC_MAX_NY)
+        return fail(HEAT_E_INVALID, "heat_step_residual_noalloc: ny=%d is beyond the fixed working memory (HEAT_NOALLOC_MAX_NY=%d)",
+                    ny, HEAT_NOALLOC_MAX_NY);
+    unsigned* scratch = nullptr;
+    int rc = scratch_for_current_device(&scratch);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    float* resid = (float*)d_residual;
+    if (nx < 3 || ny < 3) { // no interior: nothing moves, the residual is zero
+        CK(cudaMemsetAsync(resid, 0, sizeof(float), st));
+        return HEAT_OK;
+    }
+    const int col_blocks = (ny - 2 + kThreads - 1) / kThreads;
+    int row_blocks = kSlots / col_blocks;
+    if (row_blocks > nx - 2) row_blocks = nx - 2;
+    if (row_blocks > 65535) row_blocks = 65535;
+    // the arrival counter must be zero when the kernel starts, whatever an earlier call left behind
+    CK(cudaMemsetAsync(scratch + kCounter, 0, sizeof(unsigned), st));
+    const dim3 grid((unsigned)col_blocks, (unsigned)row_blocks);
+    const float* in = (const float*)d_in;
+    float* out = (float*)d_out;
+    switch (arith) {
+    case HEAT_F32_FMA: step_partials<HEAT_ARITH_F32_FMA><<<grid, kThreads, 0, st>>>(in, out, nx, ny, cx, cy, scratch, resid); break;
+    case HEAT_F32_NOFMA: step_partials<HEAT_ARITH_F32_NOFMA><<<grid, kThreads, 0, st>>>(in, out, nx, ny, cx, cy, scratch, resid); break;
+    default: step_partials<HEAT_ARITH_F64MIX><<<grid, kThreads, 0, st>>>(in, out, nx, ny, cx, cy, scratch, resid); break;
+    }
+    CK(cudaGetLastError());
     return HEAT_OK;
 }
