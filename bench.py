@@ -264,7 +264,7 @@ def run_ours(args, wl, rank, world, local_rank):
     own_lups = (min(rows_own, nx - 2) if world > 1 else nx - 2) * (ny - 2) * wl["temporal_block"]
     kernel_ms = ms / max(step_launches, 1)
     achieved = BYTES_PER_LUP * own_lups / (kernel_ms * 1e-3) / 1e9
-    kname = "heat_step_vec"
+    kname = "heat_step_tb" if wl["temporal_block"] > 1 else "heat_step_vec"
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": ncu_traffic(kname), "kernel": kname, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": BYTES_PER_LUP * own_lups,
@@ -338,6 +338,7 @@ def main():
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--arith", choices=["fma", "nofma", "f64mix"], default="fma")
     ap.add_argument("--halo", choices=["p2p", "sendrecv"], default="p2p")
+    ap.add_argument("--temporal-block", type=int, default=0, help="override the workload's updates per HBM pass (1, 2, 4)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-multi", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -347,6 +348,9 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     wl = workload(args.workload, max(world, 1) if args.impl == "ours" else max(args.gpus, 1))
+    if args.temporal_block:
+        wl["temporal_block"] = args.temporal_block
+        wl["text"] += f", {args.temporal_block} updates per HBM pass"
 
     if args.impl == "reference":
         run_reference_arm(args, wl, rank, world)

@@ -55,7 +55,7 @@ typedef struct heat_params {
     int   conv_phase;      /* HEAT_PHASE_*                                             */
     int   step_convention; /* HEAT_STEPS_*                                             */
     int   arith;           /* HEAT_F32_FMA | HEAT_F32_NOFMA | HEAT_MPI_F64MIX          */
-    int   temporal_block;  /* updates fused per pass over HBM: 1, 2 or 4               */
+    int   temporal_block;  /* updates fused per pass over HBM: 1 to 4                  */
     int   device;          /* CUDA device ordinal of this strip                        */
     int   rank, nranks;    /* row-strip decomposition: this handle owns strip `rank`   */
 } heat_params;

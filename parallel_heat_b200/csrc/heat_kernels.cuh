@@ -119,13 +119,14 @@ heat_step_generic(const float* __restrict__ in, float* __restrict__ out, int nro
 // 0 and 31 for the neighbours across the warp edge.  Requirements: pitch % 4 == 0, base
 // 16-byte aligned, columns [ny, pitch) are padding.  Ring columns (0 and ny-1) are written
 // back unchanged: both buffers always hold the same ring, so this equals "not written".
+// Rows [row_lo, row_hi) are updated (rows row_lo-1 and row_hi must exist: ring or ghost).
 //   grid.x = ceil(pitch/4 / THREADS), grid.y = number of row tiles, block = THREADS
 //   reverse != 0 walks the tiles bottom-up (alternate sweeps re-use what is left in L2).
 template <int ARITH, bool RESID, int THREADS, int UNROLL>
 __global__ void __launch_bounds__(THREADS)
-heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int nrows, int ny, int64_t pitch,
+heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo, int row_hi, int ny, int64_t pitch,
               int rows_per_tile, float cx, float cy, unsigned* __restrict__ resid, float* peer_n, float* peer_s,
-              int reverse)
+              int ghost, int reverse)
 {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -141,8 +142,8 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int nrows, 
 
     const int ntiles = gridDim.y;
     const int tile = reverse ? (ntiles - 1 - (int)blockIdx.y) : (int)blockIdx.y;
-    const int r0 = 1 + tile * rows_per_tile;
-    const int r1 = min(r0 + rows_per_tile, nrows - 1);
+    const int r0 = row_lo + tile * rows_per_tile;
+    const int r1 = min(r0 + rows_per_tile, row_hi);
 
     // which of my 4 columns are ring / padding (copied through, never updated)
     const bool kx = (col == 0) || (col >= ny - 1);
@@ -189,8 +190,9 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int nrows, 
                 if (kw) o.w = c.w;
                 if (live) {
                     st4(q, o);
-                    if (r + u == 1 && peer_n) st4(peer_n + col, o);
-                    if (r + u == nrows - 2 && peer_s) st4(peer_s + col, o);
+                    // K3: the first / last `ghost` updated rows are the neighbours' ghost rows
+                    if (peer_n && r + u < row_lo + ghost) st4(peer_n + (int64_t)(r + u - row_lo) * pitch + col, o);
+                    if (peer_s && r + u >= row_hi - ghost) st4(peer_s + (int64_t)(r + u - (row_hi - ghost)) * pitch + col, o);
                 }
                 if (RESID) {
                     m = fmaxf(m, fabsf(__fsub_rn(c.x, o.x)));
@@ -209,19 +211,104 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int nrows, 
     if (RESID) block_max_to_global(live ? m : 0.0f, resid);
 }
 
+// ------------------------------------------------------------------ K4 temporal blocking
+// T updates per pass over HBM, bit-identical to T single updates.  Pure register pipeline, no
+// shared memory, no block barrier: a warp owns 128 consecutive columns (one float4 per lane) and
+// streams down the rows; for every time level l < T it keeps the two previous rows of that level
+// (A[l], B[l]).  When level-0 row g arrives, level 1 can produce row g-1, level 2 row g-2, ...,
+// level T row g-T, which is stored.  E/W neighbours come from shuffles only, so each level loses
+// one valid column at both ends of the warp: with T <= 4 the loss stays inside lanes 0 and 31,
+// which are loaded but never stored -- warps overlap by 8 columns (column blocks of 120).
+// Rows work the same way: a tile that stores rows [r0, r1) starts reading at r0-T and runs to
+// r1+T.  Local rows 0 and nrows-1 (ring, or outermost ghost row of a strip) are copied through at
+// every level; for a ghost row that makes rows < l wrong at level l, which is why a strip keeps T
+// ghost rows and stores only [row_lo, row_hi).
+//   grid.x = ceil(ceil(pitch/120) / WARPS), grid.y = row tiles, block = 32*WARPS
+template <int ARITH, int T, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
+heat_step_tb(const float* __restrict__ in, float* __restrict__ out, int nrows, int row_lo, int row_hi, int ny,
+             int64_t pitch, int rows_per_tile, float cx, float cy, float* peer_n, float* peer_s, int reverse)
+{
+    static_assert(T >= 2 && T <= 4, "the column halo of T levels must fit in one float4 lane");
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int npitch = (int)pitch;
+    const int wcol = blockIdx.x * WARPS + (threadIdx.x >> 5);
+    const int c0 = wcol * 120 - 4;
+    if (c0 + 4 >= npitch) return; // nothing to store in this warp (warp-uniform)
+    const int col = c0 + lane * 4;
+    const bool inrange = col >= 0 && col < npitch;
+    const bool stores = inrange && lane >= 1 && lane <= 30;
+
+    const int ntiles = gridDim.y;
+    const int tile = reverse ? (ntiles - 1 - (int)blockIdx.y) : (int)blockIdx.y;
+    const int r0 = row_lo + tile * rows_per_tile;
+    const int r1 = min(r0 + rows_per_tile, row_hi);
+
+    const bool kx = (col <= 0) || (col >= ny - 1);
+    const bool ky = (col + 1 >= ny - 1);
+    const bool kz = (col + 2 >= ny - 1);
+    const bool kw = (col + 3 >= ny - 1);
+
+    const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 A[T], B[T];
+#pragma unroll
+    for (int l = 0; l < T; l++) A[l] = B[l] = zero;
+
+    const float* p = in + (inrange ? col : 0);
+    const int g0 = r0 - T, g1 = r1 + T;
+    auto load_row = [&](int g) -> float4 {
+        return (inrange && g >= 0 && g < nrows) ? ld4(p + (int64_t)g * pitch) : zero;
+    };
+    // two rows of look-ahead keep enough loads in flight (traffic is 1/T of the single-step kernel)
+    float4 nx0 = load_row(g0), nx1 = load_row(g0 + 1);
+    for (int g = g0; g < g1; g++) {
+        float4 x = nx0;
+        nx0 = nx1;
+        nx1 = load_row(g + 2 < g1 ? g + 2 : g1 - 1);
+#pragma unroll
+        for (int l = 0; l < T; l++) {
+            const int i = g - l - 1; // the row level l+1 can produce now
+            float4 y = B[l];
+            if (i > 0 && i < nrows - 1) {
+                float wl = __shfl_up_sync(FULL, B[l].w, 1);
+                float er = __shfl_down_sync(FULL, B[l].x, 1);
+                float4 o;
+                o.x = upd<ARITH>(B[l].x, A[l].x, x.x, B[l].y, wl, cx, cy);
+                o.y = upd<ARITH>(B[l].y, A[l].y, x.y, B[l].z, B[l].x, cx, cy);
+                o.z = upd<ARITH>(B[l].z, A[l].z, x.z, B[l].w, B[l].y, cx, cy);
+                o.w = upd<ARITH>(B[l].w, A[l].w, x.w, er, B[l].z, cx, cy);
+                if (!kx) y.x = o.x;
+                if (!ky) y.y = o.y;
+                if (!kz) y.z = o.z;
+                if (!kw) y.w = o.w;
+            }
+            A[l] = B[l];
+            B[l] = x;
+            x = y;
+        }
+        const int orow = g - T;
+        if (stores && orow >= r0 && orow < r1) {
+            st4(out + (int64_t)orow * pitch + col, x);
+            if (peer_n && orow < row_lo + T) st4(peer_n + (int64_t)(orow - row_lo) * pitch + col, x);
+            if (peer_s && orow >= row_hi - T) st4(peer_s + (int64_t)(orow - (row_hi - T)) * pitch + col, x);
+        }
+    }
+}
+
 // ------------------------------------------------------------------ residual of two buffers
 // max |a-b| over the interior of a strip (heat_residual(): a separate pass, not on the hot path)
 __global__ void __launch_bounds__(256)
-heat_absdiff_max(const float* __restrict__ a, const float* __restrict__ b, int nrows, int ny, int64_t pitch,
+heat_absdiff_max(const float* __restrict__ a, const float* __restrict__ b, int row_lo, int row_hi, int ny, int64_t pitch,
                  unsigned* __restrict__ resid)
 {
     float m = 0.0f;
-    const int64_t total = (int64_t)(nrows - 2) * pitch;
+    const int64_t total = (int64_t)(row_hi - row_lo) * pitch;
     for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
         const int lr = (int)(k / pitch);
         const int iy = (int)(k - (int64_t)lr * pitch);
         if (iy < ny) {
-            const int64_t idx = k + pitch; // skip local row 0
+            const int64_t idx = k + (int64_t)row_lo * pitch; // first updated row
             m = fmaxf(m, fabsf(__fsub_rn(a[idx], b[idx])));
         }
     }

@@ -82,7 +82,7 @@ def test_bad_arguments_are_rejected_with_a_message(ph):
     p = ph.default_params(nx=0)
     g = np.zeros((4, 4), np.float32)
     assert lib.heat_solve(C.byref(p), g.ctypes.data_as(C.POINTER(C.c_float)), None, None) == ph.api.E_INVALID
-    for bad in (dict(arith=7), dict(temporal_block=3), dict(rank=2, nranks=2), dict(steps=-1), dict(conv_every=-2)):
+    for bad in (dict(arith=7), dict(temporal_block=5), dict(rank=2, nranks=2), dict(steps=-1), dict(conv_every=-2)):
         h = C.c_void_p()
         p = ph.default_params(**bad)
         assert lib.heat_create(C.byref(p), C.byref(h)) == ph.api.E_INVALID, bad

@@ -270,6 +270,64 @@ def test_unconnected_strip_refuses_to_run(ph):
         assert ei.value.code == ph.api.E_STATE
 
 
+# ---------------------------------------------------------------- K4: temporal blocking
+@pytest.mark.parametrize("T", [2, 4])
+@pytest.mark.parametrize("arith", MODES)
+def test_temporal_blocking_is_bit_identical(ph, oracle, T, arith):
+    # T fused updates == T single updates, same bits, for any shape and any step count
+    for shape in [(3, 3), (5, 9), (20, 20), (33, 47), (130, 121), (131, 250), (70, 1000), (300, 1030)]:
+        u = field(shape, seed=T + shape[1])
+        for steps in (T, T + 1, 3 * T + 2, 17):
+            want, _, _ = oracle.solve(u, steps, arith=arith)
+            got, done, _ = ph.solve(u, steps, arith=arith, temporal_block=T)
+            assert done == steps
+            assert_same_bits(got, want, f"T={T} {shape} steps={steps} arith={arith}")
+
+
+@pytest.mark.parametrize("T", [2, 4])
+def test_temporal_blocking_tile_heights(ph, oracle, T, monkeypatch):
+    u = field((200, 500), seed=3)
+    want, _, _ = oracle.solve(u, 2 * T, arith=0)
+    for rpt in (1, 5, 64, 1000):
+        monkeypatch.setenv("HEAT_ROWS_PER_TILE_TB", str(rpt))
+        got, _, _ = ph.solve(u, 2 * T, arith=0, temporal_block=T)
+        assert_same_bits(got, want, f"T={T} rows_per_tile_tb={rpt}")
+
+
+@pytest.mark.parametrize("T", [2, 4])
+@pytest.mark.parametrize("phase", [0, 1])
+def test_temporal_blocking_with_convergence_check(ph, oracle, T, phase):
+    # fused passes may not swallow a checked update: same stop step, same bits
+    for shape, K in [((20, 20), 20), ((20, 20), 7), ((33, 47), 5), ((24, 40), 3)]:
+        u = ph.inidat(*shape)
+        want, wdone, wconv = oracle.solve(u, 5000, arith=2, conv_every=K, conv_phase=phase, step_convention=1)
+        got, done, conv = ph.solve(u, 5000, arith=2, conv_every=K, conv_phase=phase, step_convention=1, temporal_block=T)
+        assert (done, conv) == (wdone, wconv)
+        assert_same_bits(got, want, f"T={T} K={K} phase={phase}")
+
+
+@pytest.mark.parametrize("T", [2, 4])
+@pytest.mark.parametrize("g", [2, 3, 4])
+def test_temporal_blocking_in_strips(ph, oracle, T, g):
+    for shape in [(64, 64), (67, 250), (258, 36)]:
+        u = field(shape, seed=g * T)
+        for steps in (T, 3 * T + 1, 26):
+            want, _, _ = oracle.solve(u, steps, arith=1)
+            got, done, _ = run_strips(ph, u, g, steps, arith=1, temporal_block=T)
+            assert done == steps
+            assert_same_bits(got, want, f"T={T} {g} strips {shape} steps={steps}")
+
+
+def test_temporal_blocking_8192(ph, oracle):
+    n, steps = 8192, 8
+    with ph.HeatSolver(n, n, arith=ph.F32_FMA, temporal_block=4) as s:
+        s.init_inidat()
+        s.run(steps)
+        got = s.download()
+    want, _, _ = oracle.solve(oracle.inidat(n, n), steps, arith=0)
+    assert_same_bits(got, want, "8192^2 T=4")
+
+
 # ---------------------------------------------------------------- full-size checks
 def test_8192_bit_exact_vs_oracle_and_properties(ph, oracle):
     # BASELINE config 2's grid; the oracle does a few updates of it in seconds

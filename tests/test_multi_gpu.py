@@ -1,0 +1,94 @@
+"""Row strips over several GPUs (needs >= 2 GPUs; skipped otherwise).
+
+* one process per GPU, CUDA-IPC peer stores + device-side step flags (the bench path),
+  and the NCCL send/recv fallback -- both bit-identical to the undecomposed oracle run;
+* one process driving two GPUs (heat_connect_local across devices)."""
+import os
+import socket
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def ngpus():
+    import torch
+    return torch.cuda.device_count()
+
+
+needs2 = pytest.mark.skipif(ngpus() < 2, reason="needs 2 GPUs")
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, shape, steps, halo, params, out_path):
+    sys.path.insert(0, str(ROOT))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        import parallel_heat_b200 as ph
+        from parallel_heat_b200.strips import StripSolver
+        u = ph.inidat(*shape) if params.pop("inidat", True) else None
+        s = StripSolver(shape[0], shape[1], device=rank, halo=halo, **params)
+        s.upload(u)
+        done, conv = s.run(steps)
+        full = s.gather(0)
+        if rank == 0:
+            np.savez(out_path, full=full, done=done, conv=conv)
+        s.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@needs2
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("halo", ["p2p", "sendrecv"])
+@pytest.mark.parametrize("shape,steps,params", [
+    ((64, 64), 50, dict(arith=0)),
+    ((257, 1030), 33, dict(arith=1)),
+    ((40, 24), 100000, dict(arith=2, step_convention=1, conv_every=20, conv_phase=0)),
+    ((2048, 4096), 40, dict(arith=0)),
+])
+def test_strips_one_process_per_gpu(tmp_path, oracle, ph, halo, shape, steps, params):
+    import torch.multiprocessing as mp
+    world = min(ngpus(), 4) if shape[0] >= 64 else 2
+    out = tmp_path / "out.npz"
+    mp.spawn(_worker, args=(world, _free_port(), shape, steps, halo, dict(params), str(out)), nprocs=world, join=True)
+    r = np.load(out)
+    want, wdone, wconv = oracle.solve(oracle.inidat(*shape), steps, arith=params.get("arith", 0),
+                                      step_convention=params.get("step_convention", 0),
+                                      conv_every=params.get("conv_every", 0), conv_phase=params.get("conv_phase", 1))
+    assert (int(r["done"]), bool(r["conv"])) == (wdone, wconv)
+    assert np.array_equal(r["full"].view(np.uint32), want.view(np.uint32))
+
+
+@needs2
+def test_one_process_two_gpus(ph, oracle):
+    g = min(ngpus(), 4)
+    u = ph.inidat(300, 520)
+    ss = [ph.HeatSolver(300, 520, rank=r, nranks=g, device=r, arith=ph.F32_NOFMA) for r in range(g)]
+    try:
+        for r, s in enumerate(ss):
+            s.connect_local(ss[r - 1] if r > 0 else None, ss[r + 1] if r < g - 1 else None)
+        for s in ss:
+            s.upload(u)
+        done, _ = ph.group_run(ss, 60)
+        out = np.zeros_like(u)
+        for s in ss:
+            s.download(out)
+    finally:
+        for s in ss:
+            s.close()
+    want, _, _ = oracle.solve(u, 60, arith=1)
+    assert done == 60 and np.array_equal(out.view(np.uint32), want.view(np.uint32))
