@@ -11,6 +11,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
 
 using namespace heatk;
 
@@ -179,9 +180,11 @@ struct heat_handle {
     unsigned long long seq = 0;  // monotonic epoch for the strip flags
     int64_t launches = 0;
     int rows_per_tile = 0;
-    int rows_per_tile_tb = 64;
+    int rows_per_tile_tb = 0;     // 0 = choose per launch
     int sm_count = 148;
     // neighbours: side 0 = north (lower rows), 1 = south
+    unsigned* d_edge_count = nullptr;    // [2] edge-CTA arrival counters of the fused strip ordering
+    strip_sync sync_args = {};           // filled per pass for flag-ordered strips, else all null
     unsigned long long* flags = nullptr; // [0] written by north neighbour, [1] by south
     peer_side peer[2];
     bool connected = false;
@@ -242,6 +245,7 @@ extern "C" int heat_destroy(heat_handle* h)
     if (h->buf[1]) cudaFree(h->buf[1]);
     if (h->flags) cudaFree(h->flags);
     if (h->d_resid) cudaFree(h->d_resid);
+    if (h->d_edge_count) cudaFree(h->d_edge_count);
     if (h->h_resid) cudaFreeHost(h->h_resid);
     if (h->h_status) cudaFreeHost(h->h_status);
     if (h->ev0) cudaEventDestroy(h->ev0);
@@ -296,6 +300,7 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     CKH(cudaMalloc((void**)&h->buf[1], bytes));
     CKH(cudaMalloc((void**)&h->flags, 2 * sizeof(unsigned long long)));
     CKH(cudaMalloc((void**)&h->d_resid, sizeof(unsigned)));
+    CKH(cudaMalloc((void**)&h->d_edge_count, 2 * sizeof(unsigned)));
     CKH(cudaHostAlloc((void**)&h->h_resid, sizeof(unsigned), cudaHostAllocDefault));
     CKH(cudaHostAlloc((void**)&h->h_status, sizeof(int), cudaHostAllocMapped));
     *h->h_status = 0;
@@ -306,6 +311,7 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     CKH(cudaMemsetAsync(h->buf[1], 0, bytes, h->stream));
     CKH(cudaMemsetAsync(h->flags, 0, 2 * sizeof(unsigned long long), h->stream));
     CKH(cudaMemsetAsync(h->d_resid, 0, sizeof(unsigned), h->stream));
+    CKH(cudaMemsetAsync(h->d_edge_count, 0, 2 * sizeof(unsigned), h->stream));
     CKH(cudaEventCreate(&h->ev0));
     CKH(cudaEventCreate(&h->ev1));
     CKH(cudaEventCreateWithFlags(&h->ev_resid, cudaEventDisableTiming));
@@ -315,8 +321,7 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     CKH(cudaStreamSynchronize(h->stream));
 #undef CKH
     h->rows_per_tile = env_int("HEAT_ROWS_PER_TILE", 0);
-    h->rows_per_tile_tb = env_int("HEAT_ROWS_PER_TILE_TB", 64);
-    if (h->rows_per_tile_tb < 1) h->rows_per_tile_tb = 64;
+    h->rows_per_tile_tb = env_int("HEAT_ROWS_PER_TILE_TB", 0);
     h->serpentine = env_int("HEAT_SERPENTINE", 1) != 0;
     *out = h;
     return HEAT_OK;
@@ -345,6 +350,20 @@ static int pick_rows_per_tile(const heat_handle* h, int threads)
     return 8;
 }
 
+// how many CTAs touch the north / south neighbour (same predicate as edge_n / edge_s in the kernels)
+static void count_edge_ctas(heat_handle* h, int rows, int rpt, unsigned grid_x, unsigned tiles)
+{
+    unsigned tn = 0, ts = 0;
+    for (unsigned t = 0; t < tiles; t++) {
+        const int r0 = (int)t * rpt, r1 = (r0 + rpt < rows) ? r0 + rpt : rows; // relative to upd_lo
+        if (r0 < h->ghost) tn++;
+        if (r1 > rows - h->ghost) ts++;
+        if (r0 >= h->ghost && t + 8 < tiles) t = tiles - 9; // only the ends can qualify: skip the middle
+    }
+    h->sync_args.count_n = tn * grid_x;
+    h->sync_args.count_s = ts * grid_x;
+}
+
 template <int ARITH, bool RESID>
 static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, float* peer_n, float* peer_s, int reverse)
 {
@@ -352,10 +371,18 @@ static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, fl
     if (rows < 1 || ny < 3) return cudaSuccess; // no interior: nothing to update (ring only)
     constexpr int THREADS = 128, UNROLL = 4;
     int rpt = pick_rows_per_tile(h, THREADS);
+    if (rpt < h->ghost) rpt = h->ghost;
     if ((rows + rpt - 1) / rpt > 65535) rpt = (rows + 65534) / 65535; // grid.y limit: taller tiles
     dim3 grid((unsigned)((h->pitch / 4 + THREADS - 1) / THREADS), (unsigned)((rows + rpt - 1) / rpt));
-    heat_step_vec<ARITH, RESID, THREADS, UNROLL><<<grid, THREADS, 0, h->stream>>>(
-        in, out, h->upd_lo, h->upd_hi, ny, h->pitch, rpt, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse);
+    count_edge_ctas(h, rows, rpt, grid.x, grid.y);
+    if (h->sync_args.counters)
+        heat_step_vec<ARITH, RESID, THREADS, UNROLL, true><<<grid, THREADS, 0, h->stream>>>(
+            in, out, h->upd_lo, h->upd_hi, ny, h->pitch, rpt, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse,
+            h->sync_args);
+    else
+        heat_step_vec<ARITH, RESID, THREADS, UNROLL, false><<<grid, THREADS, 0, h->stream>>>(
+            in, out, h->upd_lo, h->upd_hi, ny, h->pitch, rpt, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse,
+            h->sync_args);
     h->launches++;
     return cudaGetLastError();
 }
@@ -367,12 +394,36 @@ static cudaError_t launch_tb_t(heat_handle* h, const float* in, float* out, floa
     const int rows = h->upd_hi - h->upd_lo, ny = h->p.ny;
     if (rows < 1 || ny < 3) return cudaSuccess;
     constexpr int WARPS = 4;
-    int rpt = h->rows_per_tile_tb;
-    if ((rows + rpt - 1) / rpt > 65535) rpt = (rows + 65534) / 65535;
     const int64_t wcols = (h->pitch + 119) / 120;
+    int rpt = h->rows_per_tile_tb;
+    if (rpt <= 0) {
+        // Tile height: a tile of R rows costs R + 3T row iterations (pipeline fill), so tall tiles
+        // waste less, but too few CTAs leave SMs idle at the end of the pass.  Minimise
+        //   (1 + 3T/R) * (1 + 0.5 / waves),   waves = CTAs / (6 resident CTAs x SMs)
+        // (measured on B200: 8192^2 prefers 48 rows, 32768^2 256 rows or more).
+        static const int cand[] = {16, 24, 32, 48, 64, 96, 128, 192, 256, 384, 512};
+        const double resident = 6.0 * h->sm_count, colblocks = (double)((wcols + WARPS - 1) / WARPS);
+        double best = 1e30;
+        rpt = 64;
+        for (int c : cand) {
+            const double waves = colblocks * ((rows + c - 1) / c) / resident;
+            const double cost = (1.0 + 3.0 * T / c) * (1.0 + 0.5 / waves);
+            if (cost < best) {
+                best = cost;
+                rpt = c;
+            }
+        }
+    }
+    if (rpt < T) rpt = T;
+    if ((rows + rpt - 1) / rpt > 65535) rpt = (rows + 65534) / 65535;
     dim3 grid((unsigned)((wcols + WARPS - 1) / WARPS), (unsigned)((rows + rpt - 1) / rpt));
-    heat_step_tb<ARITH, T, WARPS><<<grid, WARPS * 32, 0, h->stream>>>(in, out, h->nloc, h->upd_lo, h->upd_hi, ny, h->pitch, rpt,
-                                                                     h->p.cx, h->p.cy, peer_n, peer_s, reverse);
+    count_edge_ctas(h, rows, rpt, grid.x, grid.y);
+    if (h->sync_args.counters)
+        heat_step_tb<ARITH, T, WARPS, true><<<grid, WARPS * 32, 0, h->stream>>>(in, out, h->nloc, h->upd_lo, h->upd_hi, ny, h->pitch,
+                                                                               rpt, h->p.cx, h->p.cy, peer_n, peer_s, reverse, h->sync_args);
+    else
+        heat_step_tb<ARITH, T, WARPS, false><<<grid, WARPS * 32, 0, h->stream>>>(in, out, h->nloc, h->upd_lo, h->upd_hi, ny, h->pitch,
+                                                                                rpt, h->p.cx, h->p.cy, peer_n, peer_s, reverse, h->sync_args);
     h->launches++;
     return cudaGetLastError();
 }
@@ -422,28 +473,33 @@ static int enqueue_update(heat_handle* h, bool resid, int fused = 1)
             // neighbour's epoch `seq` (its previous update, or its upload) must be complete
             for (int side = 0; side < 2; side++)
                 if (h->local_nb[side]) CK(cudaStreamWaitEvent(h->stream, h->local_nb[side]->ev_done[h->seq & 1], 0));
-        } else {
-            heat_wait<<<1, 32, 0, h->stream>>>(has_n ? &h->flags[0] : nullptr, has_s ? &h->flags[1] : nullptr, h->seq,
-                                               WAIT_TIMEOUT_NS, h->d_status);
-            h->launches++;
         }
         // my first owned row (local row 1) is the north neighbour's bottom ghost row, and vice versa
         if (has_n) pn = h->peer[0].buf[1 - h->cur] + (int64_t)(h->peer[0].nloc - h->ghost) * h->pitch;
         if (has_s) ps = h->peer[1].buf[1 - h->cur];
     }
     if (resid) CK(cudaMemsetAsync(h->d_resid, 0, sizeof(unsigned), h->stream));
+    // flag-ordered strips (one process per GPU): the wait and the signal are fused into the pass
+    h->sync_args = strip_sync{};
+    if (strips && !local) {
+        strip_sync& sy = h->sync_args;
+        sy.wait_n = has_n ? &h->flags[0] : nullptr;
+        sy.wait_s = has_s ? &h->flags[1] : nullptr;
+        sy.wait_value = h->seq;
+        sy.sig_n = has_n ? h->peer[0].flag : nullptr;
+        sy.sig_s = has_s ? h->peer[1].flag : nullptr;
+        sy.sig_value = h->seq + 1;
+        sy.counters = h->d_edge_count;
+        sy.status = h->d_status;
+        sy.timeout_ns = WAIT_TIMEOUT_NS;
+    }
     const int reverse = h->serpentine ? (int)(h->sweeps & 1) : 0;
     h->sweeps++;
     if (fused > 1) CK(launch_tb(h, fused, in, out, pn, ps, reverse));
     else CK(launch_step(h, resid, in, out, pn, ps, reverse));
     h->seq++;
     if (strips) {
-        if (local) {
-            CK(cudaEventRecord(h->ev_done[h->seq & 1], h->stream));
-        } else {
-            heat_signal<<<1, 32, 0, h->stream>>>(has_n ? h->peer[0].flag : nullptr, has_s ? h->peer[1].flag : nullptr, h->seq);
-            h->launches++;
-        }
+        if (local) CK(cudaEventRecord(h->ev_done[h->seq & 1], h->stream));
     }
     CK(cudaGetLastError());
     h->cur = 1 - h->cur;
@@ -639,9 +695,10 @@ static int upload_from(heat_handle* h, const void* src, cudaMemcpyKind kind)
         return fail(HEAT_E_STATE, "heat_upload: connect the strips first");
     CK(cudaSetDevice(h->p.device));
     const float* rows = (const float*)src + (size_t)h->lo * h->p.ny;
-    for (int b = 0; b < 2; b++) // C:197-198: the initial field goes into both buffers
-        CK(cudaMemcpy2DAsync(h->buf[b], h->pitch * sizeof(float), rows, (size_t)h->p.ny * sizeof(float),
-                             (size_t)h->p.ny * sizeof(float), h->nloc, kind, h->stream));
+    // C:197-198: the initial field goes into both buffers -- over PCIe once, the second copy on the device
+    CK(cudaMemcpy2DAsync(h->buf[0], h->pitch * sizeof(float), rows, (size_t)h->p.ny * sizeof(float),
+                         (size_t)h->p.ny * sizeof(float), h->nloc, kind, h->stream));
+    CK(cudaMemcpyAsync(h->buf[1], h->buf[0], (size_t)h->nloc * h->pitch * sizeof(float), cudaMemcpyDeviceToDevice, h->stream));
     return after_upload(h);
 }
 
@@ -688,13 +745,28 @@ extern "C" int heat_solve(const heat_params* p, float* grid, int* updates_done, 
 {
     if (!grid) return fail(HEAT_E_INVALID, "heat_solve: null grid");
     if (p && p->nranks != 1) return fail(HEAT_E_INVALID, "heat_solve: one strip only (use the handle API for strips)");
+    const bool timing = env_int("HEAT_TIMING", 0) != 0;
+    auto now = [] {
+        struct timespec ts;
+        clock_gettime(CLOCK_MONOTONIC, &ts);
+        return ts.tv_sec + 1e-9 * ts.tv_nsec;
+    };
+    const double t0 = now();
     heat_handle* h = nullptr;
     int rc = heat_create(p, &h);
     if (rc) return rc;
+    const double t1 = now();
     rc = heat_upload(h, grid);
+    const double t2 = now();
     if (!rc) rc = heat_run(h, p->steps, updates_done, converged);
+    const double t3 = now();
     if (!rc) rc = heat_download(h, grid);
+    const double t4 = now();
+    const float loop_ms = h->last_ms;
     heat_destroy(h);
+    if (timing)
+        fprintf(stderr, "heat_solve: create %.3f ms, upload %.3f ms, run %.3f ms (device loop %.3f ms), download %.3f ms, destroy %.3f ms\n",
+                (t1 - t0) * 1e3, (t2 - t1) * 1e3, (t3 - t2) * 1e3, loop_ms, (t4 - t3) * 1e3, (now() - t4) * 1e3);
     return rc;
 }
 

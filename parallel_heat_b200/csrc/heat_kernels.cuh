@@ -112,6 +112,81 @@ heat_step_generic(const float* __restrict__ in, float* __restrict__ out, int nro
     if (RESID) block_max_to_global(m, resid);
 }
 
+// ------------------------------------------------------------------ strip ordering inside the update kernels
+// One process per GPU: neighbours are ordered by step flags in each other's memory (see
+// heat_signal/heat_wait below for the stand-alone versions).  Fused into the update kernels so
+// that a pass costs one launch: only the CTAs of the tiles that touch a neighbour's data
+// (they read ghost rows and store the neighbour's ghost rows) wait for the neighbour's flag,
+// interior tiles start at once; when the last of those edge CTAs is done, it raises the
+// neighbour's flag.  All pointers null = single strip / event-ordered strips: no code runs.
+struct strip_sync {
+    const unsigned long long* wait_n; // my slot written by the north neighbour
+    const unsigned long long* wait_s;
+    unsigned long long wait_value;    // epoch the neighbours must have completed
+    unsigned long long* sig_n;        // the north neighbour's slot for me
+    unsigned long long* sig_s;
+    unsigned long long sig_value;
+    unsigned* counters;               // [0] north-edge CTAs done, [1] south-edge CTAs done
+    unsigned count_n, count_s;        // how many CTAs touch the north / south neighbour
+    int* status;                      // raised when a wait times out
+    unsigned long long timeout_ns;
+};
+
+__device__ __forceinline__ void spin_until(const unsigned long long* f, unsigned long long value,
+                                           unsigned long long timeout_ns, int* status)
+{
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    unsigned spins = 0;
+    for (;;) {
+        unsigned long long v;
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+        if (v >= value) return;
+        if ((++spins & 255u) == 0) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (t - t0 > timeout_ns) {
+                *status = 1;
+                __threadfence_system();
+                return;
+            }
+        }
+        __nanosleep(32);
+    }
+}
+
+// all threads of the CTA call these (block barrier inside); edge_n/edge_s are CTA-uniform
+__device__ __forceinline__ void strip_wait(const strip_sync& sy, bool edge_n, bool edge_s)
+{
+    const bool wn = edge_n && sy.wait_n, ws = edge_s && sy.wait_s;
+    if (wn || ws) {
+        if (threadIdx.x == 0) {
+            if (wn) spin_until(sy.wait_n, sy.wait_value, sy.timeout_ns, sy.status);
+            if (ws) spin_until(sy.wait_s, sy.wait_value, sy.timeout_ns, sy.status);
+        }
+        __syncthreads();
+    }
+}
+
+__device__ __forceinline__ void strip_signal(const strip_sync& sy, bool edge_n, bool edge_s)
+{
+    const bool sn = edge_n && sy.sig_n, ss = edge_s && sy.sig_s;
+    if (sn || ss) {
+        __syncthreads(); // every thread's stores (local and peer) are issued
+        if (threadIdx.x == 0) {
+            __threadfence_system();
+            if (sn && atomicAdd(&sy.counters[0], 1u) == sy.count_n - 1) {
+                sy.counters[0] = 0;
+                asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(sy.sig_n), "l"(sy.sig_value) : "memory");
+            }
+            if (ss && atomicAdd(&sy.counters[1], 1u) == sy.count_s - 1) {
+                sy.counters[1] = 0;
+                asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(sy.sig_s), "l"(sy.sig_value) : "memory");
+            }
+        }
+    }
+}
+
 // ------------------------------------------------------------------ K1/K2 vector row streaming
 // Each thread owns 4 consecutive columns (one float4) and walks down `rows_per_tile`
 // rows keeping the N / C / S rows in registers: per row one LDG.128, one STG.128, two
@@ -122,28 +197,32 @@ heat_step_generic(const float* __restrict__ in, float* __restrict__ out, int nro
 // Rows [row_lo, row_hi) are updated (rows row_lo-1 and row_hi must exist: ring or ghost).
 //   grid.x = ceil(pitch/4 / THREADS), grid.y = number of row tiles, block = THREADS
 //   reverse != 0 walks the tiles bottom-up (alternate sweeps re-use what is left in L2).
-template <int ARITH, bool RESID, int THREADS, int UNROLL>
-__global__ void __launch_bounds__(THREADS)
+template <int ARITH, bool RESID, int THREADS, int UNROLL, bool SYNC>
+// the plain single-strip update is held to 48 registers (40 warps per SM), the variants with the
+// residual or the strip flags to 56 (36 warps), the double-precision mode to 64
+__global__ void __launch_bounds__(THREADS, (ARITH == HEAT_ARITH_F64MIX ? 1024 : (SYNC || RESID) ? 1152 : 1280) / THREADS)
 heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo, int row_hi, int ny, int64_t pitch,
               int rows_per_tile, float cx, float cy, unsigned* __restrict__ resid, float* peer_n, float* peer_s,
-              int ghost, int reverse)
+              int ghost, int reverse, strip_sync sy)
 {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int npitch = (int)pitch;
     int col = (blockIdx.x * THREADS + threadIdx.x) * 4;
-    // whole warp beyond the row: nothing to do (warp-uniform exit, before any shuffle)
-    if (col - lane * 4 >= npitch) {
-        if (RESID) block_max_to_global(0.0f, resid);
-        return;
-    }
-    const bool live = col < npitch;
-    if (!live) col = npitch - 4; // keep the lane in bounds for loads; it never stores
 
     const int ntiles = gridDim.y;
     const int tile = reverse ? (ntiles - 1 - (int)blockIdx.y) : (int)blockIdx.y;
     const int r0 = row_lo + tile * rows_per_tile;
     const int r1 = min(r0 + rows_per_tile, row_hi);
+    // tiles that touch a neighbour strip's data: they read ghost rows / store its ghost rows
+    const bool edge_n = r0 < row_lo + ghost, edge_s = r1 > row_hi - ghost;
+    if (SYNC) strip_wait(sy, edge_n, edge_s);
+
+    float m = 0.0f;
+    // a whole warp beyond the row has nothing to do (warp-uniform, so the shuffles stay converged)
+    const bool live = col < npitch;
+    if (col - lane * 4 < npitch) {
+    if (!live) col = npitch - 4; // keep the lane in bounds for loads; it never stores
 
     // which of my 4 columns are ring / padding (copied through, never updated)
     const bool kx = (col == 0) || (col >= ny - 1);
@@ -160,7 +239,6 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
     float4 c = ld4(p + pitch);
     float ec = edge_lane ? p[pitch + edge_off] : 0.0f;
     p += 2 * pitch; // points at row r+1 (the S row of the first output row)
-    float m = 0.0f;
 
     for (int r = r0; r < r1; r += UNROLL) {
         float4 s[UNROLL];
@@ -208,7 +286,9 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
         }
         p += (int64_t)UNROLL * pitch;
     }
+    } // warp inside the row
     if (RESID) block_max_to_global(live ? m : 0.0f, resid);
+    if (SYNC) strip_signal(sy, edge_n, edge_s);
 }
 
 // ------------------------------------------------------------------ K4 temporal blocking
@@ -224,10 +304,86 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
 // every level; for a ghost row that makes rows < l wrong at level l, which is why a strip keeps T
 // ghost rows and stores only [row_lo, row_hi).
 //   grid.x = ceil(ceil(pitch/120) / WARPS), grid.y = row tiles, block = 32*WARPS
-template <int ARITH, int T, int WARPS>
+// Update of a float4 whose four columns and three rows are all interior: no ring fix-ups.
+template <int ARITH>
+__device__ __forceinline__ float4 upd4(const float4& c, const float4& n, const float4& s, float cx, float cy)
+{
+    const float wl = __shfl_up_sync(0xffffffffu, c.w, 1);
+    const float er = __shfl_down_sync(0xffffffffu, c.x, 1);
+    float4 o;
+    o.x = upd<ARITH>(c.x, n.x, s.x, c.y, wl, cx, cy);
+    o.y = upd<ARITH>(c.y, n.y, s.y, c.z, c.x, cx, cy);
+    o.z = upd<ARITH>(c.z, n.z, s.z, c.w, c.y, cx, cy);
+    o.w = upd<ARITH>(c.w, n.w, s.w, er, c.z, cx, cy);
+    return o;
+}
+
+// Fast path of K4 for a warp whose 128 columns hold no ring/padding column and whose tile is far
+// enough from local rows 0 and nrows-1 (and from a neighbour strip's rows): no row or column
+// special cases, no peer stores, no address clamping.
+// Every level keeps THREE consecutive rows of its input (S[l][0..2]); the levels are evaluated
+// from the last to the first, each reading what the level below produced in the PREVIOUS
+// iteration, so the T updates of one iteration are independent of each other (ILP = T) and the
+// result of level l is written straight over the oldest row of level l+1.  With the row loop
+// unrolled by 3 the slot indices are compile-time constants and no register is ever moved.
+// Level l emits row g-(2l+1) of level l+1 in the iteration that loads level-0 row g, so the
+// first 3T iterations (starting one row early, at r0-T-1, to make that a multiple of 3) only
+// fill the pipeline and every later iteration stores one row.
+//   requires r0-T-1 >= 0 and r1+2T+1 <= nrows-1 (all rows touched exist; none is a ring row)
+template <int ARITH, int T, bool STORE>
+__device__ __forceinline__ void tb_fast_3(float4 (&S)[T][3], float4 (&P)[3], const float*& pl, float*& ps, int64_t pitch,
+                                          bool stores, int& left, float cx, float cy)
+{
+#pragma unroll
+    for (int ph = 0; ph < 3; ph++) {
+#pragma unroll
+        for (int l = T - 1; l >= 1; l--) {
+            // rows of level l in age order: S[l][ph] (oldest), S[l][ph+1], S[l][ph+2] (newest)
+            const float4 y = upd4<ARITH>(S[l][(ph + 1) % 3], S[l][ph], S[l][(ph + 2) % 3], cx, cy);
+            if (l == T - 1) {
+                if (STORE) {
+                    if (stores && left > 0) st4(ps, y);
+                    ps += pitch;
+                    left--;
+                }
+            } else {
+                S[l + 1][ph] = y;
+            }
+        }
+        S[0][ph] = P[ph]; // the next level-0 row; its slot held the row three above
+        P[ph] = ld4(pl);
+        pl += pitch;
+        S[1][ph] = upd4<ARITH>(S[0][(ph + 2) % 3], S[0][(ph + 1) % 3], S[0][ph], cx, cy);
+    }
+}
+
+template <int ARITH, int T>
+__device__ __forceinline__ void tb_fast(const float* __restrict__ in, float* __restrict__ out, int64_t pitch, int col,
+                                        bool stores, int r0, int r1, float cx, float cy)
+{
+    const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 S[T][3], P[3];
+#pragma unroll
+    for (int l = 0; l < T; l++) S[l][0] = S[l][1] = S[l][2] = zero;
+    const float* pl = in + (int64_t)(r0 - T - 1) * pitch + col; // next level-0 row to load
+    float* ps = out + (int64_t)r0 * pitch + col;                 // next row to store
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+        P[j] = ld4(pl);
+        pl += pitch;
+    }
+    int left = r1 - r0;
+    // pipeline fill: 3T iterations, nothing to store yet
+    for (int w = 0; w < T; w++) tb_fast_3<ARITH, T, false>(S, P, pl, ps, pitch, stores, left, cx, cy);
+    // steady state: one stored row per iteration
+    while (left > 0) tb_fast_3<ARITH, T, true>(S, P, pl, ps, pitch, stores, left, cx, cy);
+}
+
+template <int ARITH, int T, int WARPS, bool SYNC>
 __global__ void __launch_bounds__(WARPS * 32)
 heat_step_tb(const float* __restrict__ in, float* __restrict__ out, int nrows, int row_lo, int row_hi, int ny,
-             int64_t pitch, int rows_per_tile, float cx, float cy, float* peer_n, float* peer_s, int reverse)
+             int64_t pitch, int rows_per_tile, float cx, float cy, float* peer_n, float* peer_s, int reverse,
+             strip_sync sy)
 {
     static_assert(T >= 2 && T <= 4, "the column halo of T levels must fit in one float4 lane");
     const unsigned FULL = 0xffffffffu;
@@ -235,7 +391,6 @@ heat_step_tb(const float* __restrict__ in, float* __restrict__ out, int nrows, i
     const int npitch = (int)pitch;
     const int wcol = blockIdx.x * WARPS + (threadIdx.x >> 5);
     const int c0 = wcol * 120 - 4;
-    if (c0 + 4 >= npitch) return; // nothing to store in this warp (warp-uniform)
     const int col = c0 + lane * 4;
     const bool inrange = col >= 0 && col < npitch;
     const bool stores = inrange && lane >= 1 && lane <= 30;
@@ -244,12 +399,23 @@ heat_step_tb(const float* __restrict__ in, float* __restrict__ out, int nrows, i
     const int tile = reverse ? (ntiles - 1 - (int)blockIdx.y) : (int)blockIdx.y;
     const int r0 = row_lo + tile * rows_per_tile;
     const int r1 = min(r0 + rows_per_tile, row_hi);
+    const bool edge_n = r0 < row_lo + T, edge_s = r1 > row_hi - T;
+    if (SYNC) strip_wait(sy, edge_n, edge_s);
+    if (c0 + 4 < npitch) { // else: nothing to store in this warp (warp-uniform)
 
     const bool kx = (col <= 0) || (col >= ny - 1);
     const bool ky = (col + 1 >= ny - 1);
     const bool kz = (col + 2 >= ny - 1);
     const bool kw = (col + 3 >= ny - 1);
 
+    // interior tile and no ring/padding/outside column in the whole warp: nothing special to do
+    // (the extra margin also keeps such a tile clear of the rows a neighbour strip receives)
+    const bool plain_rows = (r0 - T - 1 >= 1) && (r1 + 2 * T + 4 <= nrows - 1) && (!peer_n || r0 >= row_lo + T) &&
+                            (!peer_s || r1 <= row_hi - T);
+    const bool plain_warp = __all_sync(FULL, inrange && !(kx || ky || kz || kw));
+    if (plain_rows && plain_warp) {
+        tb_fast<ARITH, T>(in, out, pitch, col, stores, r0, r1, cx, cy);
+    } else {
     const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
     float4 A[T], B[T];
 #pragma unroll
@@ -294,6 +460,9 @@ heat_step_tb(const float* __restrict__ in, float* __restrict__ out, int nrows, i
             if (peer_s && orow >= row_hi - T) st4(peer_s + (int64_t)(orow - (row_hi - T)) * pitch + col, x);
         }
     }
+    } // generic path
+    } // warp has columns to store
+    if (SYNC) strip_signal(sy, edge_n, edge_s);
 }
 
 // ------------------------------------------------------------------ residual of two buffers

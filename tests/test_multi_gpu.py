@@ -32,10 +32,11 @@ def _free_port():
 def _worker(rank, world, port, shape, steps, halo, params, out_path):
     sys.path.insert(0, str(ROOT))
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    rdzv = "file://" + out_path + ".rdzv"  # a file store: no TCP port to collide on
     import torch
     import torch.distributed as dist
     torch.cuda.set_device(rank)
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    dist.init_process_group("nccl", init_method=rdzv, rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
         import parallel_heat_b200 as ph
         from parallel_heat_b200.strips import StripSolver

@@ -81,7 +81,8 @@ class NumpyRows:
 def _worker(rank, world, port, shape, steps, params, out_path):
     sys.path.insert(0, str(ROOT))
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
-    dist.init_process_group("gloo", rank=rank, world_size=world)
+    rdzv = "file://" + out_path + ".rdzv"  # a file store: no TCP port to collide on
+    dist.init_process_group("gloo", init_method=rdzv, rank=rank, world_size=world)
     try:
         from oracle import pyoracle as O
         from parallel_heat_b200.strips import StripSolver
