@@ -187,6 +187,22 @@ __device__ __forceinline__ void strip_signal(const strip_sync& sy, bool edge_n, 
     }
 }
 
+// Which row tile a CTA works on.  Plain sweeps go top-down or (reverse) bottom-up.  With strip
+// flags the two edge tiles are handed to the first CTAs of the grid in either direction: their
+// system-scope fence + flag store (a few microseconds behind an NVLink round trip) then overlaps
+// with the rest of the pass instead of trailing it, and the neighbour's flag is long there when
+// the next pass starts.
+template <bool SYNC>
+__device__ __forceinline__ int tile_of_block(int by, int ntiles, int reverse)
+{
+    if (SYNC && ntiles > 2) {
+        if (by == 0) return 0;
+        if (by == 1) return ntiles - 1;
+        return reverse ? (ntiles - by) : (by - 1);
+    }
+    return reverse ? (ntiles - 1 - by) : by;
+}
+
 // ------------------------------------------------------------------ K1/K2 vector row streaming
 // Each thread owns 4 consecutive columns (one float4) and walks down `rows_per_tile`
 // rows keeping the N / C / S rows in registers: per row one LDG.128, one STG.128, two
@@ -211,7 +227,7 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
     int col = (blockIdx.x * THREADS + threadIdx.x) * 4;
 
     const int ntiles = gridDim.y;
-    const int tile = reverse ? (ntiles - 1 - (int)blockIdx.y) : (int)blockIdx.y;
+    const int tile = tile_of_block<SYNC>((int)blockIdx.y, ntiles, reverse);
     const int r0 = row_lo + tile * rows_per_tile;
     const int r1 = min(r0 + rows_per_tile, row_hi);
     // tiles that touch a neighbour strip's data: they read ghost rows / store its ghost rows
@@ -240,6 +256,47 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
     float ec = edge_lane ? p[pitch + edge_off] : 0.0f;
     p += 2 * pitch; // points at row r+1 (the S row of the first output row)
 
+    // Almost every warp takes this branch: no ring or padding column among its 128 columns, a full
+    // tile, no neighbour strip's rows to store.  Same arithmetic, none of the special cases.
+    const bool plain_warp = __all_sync(FULL, live && !(kx || ky || kz || kw));
+    const bool plain_tile = (r1 - r0 == rows_per_tile) && (rows_per_tile % UNROLL == 0) && !(peer_n && edge_n) &&
+                            !(peer_s && edge_s);
+    if (plain_warp && plain_tile) {
+        const bool el = (lane == 0) || (lane == 31);
+        for (int r = r0; r < r1; r += UNROLL) {
+            float4 s[UNROLL];
+            float es[UNROLL];
+#pragma unroll
+            for (int u = 0; u < UNROLL; u++) {
+                s[u] = ld4(p + (int64_t)u * pitch);
+                es[u] = el ? p[(int64_t)u * pitch + edge_off] : 0.0f;
+            }
+#pragma unroll
+            for (int u = 0; u < UNROLL; u++) {
+                float wl = __shfl_up_sync(FULL, c.w, 1);
+                float er = __shfl_down_sync(FULL, c.x, 1);
+                if (lane == 0) wl = ec;
+                if (lane == 31) er = ec;
+                float4 o;
+                o.x = upd<ARITH>(c.x, n.x, s[u].x, c.y, wl, cx, cy);
+                o.y = upd<ARITH>(c.y, n.y, s[u].y, c.z, c.x, cx, cy);
+                o.z = upd<ARITH>(c.z, n.z, s[u].z, c.w, c.y, cx, cy);
+                o.w = upd<ARITH>(c.w, n.w, s[u].w, er, c.z, cx, cy);
+                st4(q, o);
+                if (RESID) {
+                    m = fmaxf(m, fabsf(__fsub_rn(c.x, o.x)));
+                    m = fmaxf(m, fabsf(__fsub_rn(c.y, o.y)));
+                    m = fmaxf(m, fabsf(__fsub_rn(c.z, o.z)));
+                    m = fmaxf(m, fabsf(__fsub_rn(c.w, o.w)));
+                }
+                n = c;
+                c = s[u];
+                ec = es[u];
+                q += pitch;
+            }
+            p += (int64_t)UNROLL * pitch;
+        }
+    } else
     for (int r = r0; r < r1; r += UNROLL) {
         float4 s[UNROLL];
         float es[UNROLL];
@@ -396,7 +453,7 @@ heat_step_tb(const float* __restrict__ in, float* __restrict__ out, int nrows, i
     const bool stores = inrange && lane >= 1 && lane <= 30;
 
     const int ntiles = gridDim.y;
-    const int tile = reverse ? (ntiles - 1 - (int)blockIdx.y) : (int)blockIdx.y;
+    const int tile = tile_of_block<SYNC>((int)blockIdx.y, ntiles, reverse);
     const int r0 = row_lo + tile * rows_per_tile;
     const int r1 = min(r0 + rows_per_tile, row_hi);
     const bool edge_n = r0 < row_lo + T, edge_s = r1 > row_hi - T;
