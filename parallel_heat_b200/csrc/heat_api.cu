@@ -398,17 +398,22 @@ static cudaError_t launch_tb_t(heat_handle* h, const float* in, float* out, floa
     int rpt = h->rows_per_tile_tb;
     if (rpt <= 0) {
         // Tile height: a tile of R rows costs R + 3T row iterations (pipeline fill), so tall tiles
-        // waste less, but too few CTAs leave SMs idle at the end of the pass.  Minimise
-        //   (1 + 3T/R) * (1 + 0.5 / waves),   waves = CTAs / (6 resident CTAs x SMs)
-        // (measured on B200: 8192^2 prefers 48 rows, 32768^2 256 rows or more).
-        static const int cand[] = {16, 24, 32, 48, 64, 96, 128, 192, 256, 384, 512};
-        const double resident = 6.0 * h->sm_count, colblocks = (double)((wcols + WARPS - 1) / WARPS);
-        double best = 1e30;
+        // waste less; but the CTAs run in rounds of (resident CTAs per SM x SMs), and a last round
+        // that is nearly empty costs as much as a full one.  Minimise rounds * (R + 3T).
+        // (B200, 8192^2, T=4: 168 rows = exactly one round of 882 CTAs.)
+        int per_sm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, heat_step_tb<ARITH, T, WARPS, false>, WARPS * 32, 0) != cudaSuccess ||
+            per_sm < 1) {
+            cudaGetLastError();
+            per_sm = 6;
+        }
+        const long long resident = (long long)per_sm * h->sm_count, colblocks = (wcols + WARPS - 1) / WARPS;
+        long long best = -1;
         rpt = 64;
-        for (int c : cand) {
-            const double waves = colblocks * ((rows + c - 1) / c) / resident;
-            const double cost = (1.0 + 3.0 * T / c) * (1.0 + 0.5 / waves);
-            if (cost < best) {
+        for (int c = 16; c <= 4096 && c < rows + 8; c += 8) {
+            const long long ctas = colblocks * ((rows + c - 1) / c);
+            const long long cost = ((ctas + resident - 1) / resident) * ((c < rows ? c : rows) + 3 * T);
+            if (best < 0 || cost < best) {
                 best = cost;
                 rpt = c;
             }
