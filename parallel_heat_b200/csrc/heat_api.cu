@@ -398,9 +398,11 @@ static cudaError_t launch_tb_t(heat_handle* h, const float* in, float* out, floa
     int rpt = h->rows_per_tile_tb;
     if (rpt <= 0) {
         // Tile height: a tile of R rows costs R + 3T row iterations (pipeline fill), so tall tiles
-        // waste less; but the CTAs run in rounds of (resident CTAs per SM x SMs), and a last round
-        // that is nearly empty costs as much as a full one.  Minimise rounds * (R + 3T).
-        // (B200, 8192^2, T=4: 168 rows = exactly one round of 882 CTAs.)
+        // waste less -- but the resident CTAs should work on a compact band of rows (DRAM page / TLB
+        // locality, and the next pass finds the end of this one in L2).  Measured on B200 (T=4):
+        // best R = 48 / 96 / 128-192 / 128-256 rows at 8192^2 / 16384^2 / 32768^2 / 65536^2, i.e. the
+        // band of all resident CTAs is about 2400 rows tall whatever the row length.  Modelling the
+        // CTAs as rounds of `resident` (R = 168 at 8192^2: one exact round) was 12 % slower.
         int per_sm = 0;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, heat_step_tb<ARITH, T, WARPS, false>, WARPS * 32, 0) != cudaSuccess ||
             per_sm < 1) {
@@ -408,16 +410,12 @@ static cudaError_t launch_tb_t(heat_handle* h, const float* in, float* out, floa
             per_sm = 6;
         }
         const long long resident = (long long)per_sm * h->sm_count, colblocks = (wcols + WARPS - 1) / WARPS;
-        long long best = -1;
-        rpt = 64;
-        for (int c = 16; c <= 4096 && c < rows + 8; c += 8) {
-            const long long ctas = colblocks * ((rows + c - 1) / c);
-            const long long cost = ((ctas + resident - 1) / resident) * ((c < rows ? c : rows) + 3 * T);
-            if (best < 0 || cost < best) {
-                best = cost;
-                rpt = c;
-            }
-        }
+        // (multiples of 3: the kernel's row loop is unrolled by 3)
+        rpt = (int)((2400 * colblocks / resident + 12) / 24 * 24);
+        if (rpt < 24) rpt = 24;
+        if (rpt > 264) rpt = 264;
+        // small grids: at least two CTAs per SM before anything else
+        while (rpt > 12 && colblocks * ((rows + rpt - 1) / rpt) < 2LL * h->sm_count) rpt -= 6;
     }
     if (rpt < T) rpt = T;
     if ((rows + rpt - 1) / rpt > 65535) rpt = (rows + 65534) / 65535;

@@ -387,7 +387,12 @@ __device__ __forceinline__ float4 upd4(const float4& c, const float4& n, const f
 // first 3T iterations (starting one row early, at r0-T-1, to make that a multiple of 3) only
 // fill the pipeline and every later iteration stores one row.
 //   requires r0-T-1 >= 0 and r1+2T+1 <= nrows-1 (all rows touched exist; none is a ring row)
-template <int ARITH, int T, bool STORE>
+// Three iterations (one turn of the slot rotation).  LMAX = number of levels that compute: while
+// the pipeline fills, level l has nothing useful to do before iteration 3(l+1) (level l+1 first
+// needs the OLDEST of three rows), so the fill groups run with LMAX = 0, 1, .. T-1: 18 instead of
+// 48 level-steps for T=4.  (The drain has no such slack: the last store needs the row the level
+// below emitted one iteration earlier.)
+template <int ARITH, int T, bool STORE, int LMAX>
 __device__ __forceinline__ void tb_fast_3(float4 (&S)[T][3], float4 (&P)[3], const float*& pl, float*& ps, int64_t pitch,
                                           bool stores, int& left, float cx, float cy)
 {
@@ -395,22 +400,24 @@ __device__ __forceinline__ void tb_fast_3(float4 (&S)[T][3], float4 (&P)[3], con
     for (int ph = 0; ph < 3; ph++) {
 #pragma unroll
         for (int l = T - 1; l >= 1; l--) {
-            // rows of level l in age order: S[l][ph] (oldest), S[l][ph+1], S[l][ph+2] (newest)
-            const float4 y = upd4<ARITH>(S[l][(ph + 1) % 3], S[l][ph], S[l][(ph + 2) % 3], cx, cy);
-            if (l == T - 1) {
-                if (STORE) {
-                    if (stores && left > 0) st4(ps, y);
-                    ps += pitch;
-                    left--;
+            if (l < LMAX) {
+                // rows of level l in age order: S[l][ph] (oldest), S[l][ph+1], S[l][ph+2] (newest)
+                const float4 y = upd4<ARITH>(S[l][(ph + 1) % 3], S[l][ph], S[l][(ph + 2) % 3], cx, cy);
+                if (l == T - 1) {
+                    if (STORE) {
+                        if (stores && left > 0) st4(ps, y);
+                        ps += pitch;
+                        left--;
+                    }
+                } else {
+                    S[l + 1][ph] = y;
                 }
-            } else {
-                S[l + 1][ph] = y;
             }
         }
         S[0][ph] = P[ph]; // the next level-0 row; its slot held the row three above
         P[ph] = ld4(pl);
         pl += pitch;
-        S[1][ph] = upd4<ARITH>(S[0][(ph + 2) % 3], S[0][(ph + 1) % 3], S[0][ph], cx, cy);
+        if (LMAX >= 1) S[1][ph] = upd4<ARITH>(S[0][(ph + 2) % 3], S[0][(ph + 1) % 3], S[0][ph], cx, cy);
     }
 }
 
@@ -430,14 +437,17 @@ __device__ __forceinline__ void tb_fast(const float* __restrict__ in, float* __r
         pl += pitch;
     }
     int left = r1 - r0;
-    // pipeline fill: 3T iterations, nothing to store yet
-    for (int w = 0; w < T; w++) tb_fast_3<ARITH, T, false>(S, P, pl, ps, pitch, stores, left, cx, cy);
+    // pipeline fill: 3T iterations, nothing to store yet, level l starts in group l+1
+    tb_fast_3<ARITH, T, false, 0>(S, P, pl, ps, pitch, stores, left, cx, cy);
+    tb_fast_3<ARITH, T, false, 1>(S, P, pl, ps, pitch, stores, left, cx, cy);
+    if constexpr (T >= 3) tb_fast_3<ARITH, T, false, 2>(S, P, pl, ps, pitch, stores, left, cx, cy);
+    if constexpr (T >= 4) tb_fast_3<ARITH, T, false, 3>(S, P, pl, ps, pitch, stores, left, cx, cy);
     // steady state: one stored row per iteration
-    while (left > 0) tb_fast_3<ARITH, T, true>(S, P, pl, ps, pitch, stores, left, cx, cy);
+    while (left > 0) tb_fast_3<ARITH, T, true, T>(S, P, pl, ps, pitch, stores, left, cx, cy);
 }
 
 template <int ARITH, int T, int WARPS, bool SYNC>
-__global__ void __launch_bounds__(WARPS * 32)
+__global__ void __launch_bounds__(WARPS * 32, (ARITH == HEAT_ARITH_F64MIX ? 20 : 28) / WARPS) // <= 72 regs (F32): 7 CTAs of 4 warps
 heat_step_tb(const float* __restrict__ in, float* __restrict__ out, int nrows, int row_lo, int row_hi, int ny,
              int64_t pitch, int rows_per_tile, float cx, float cy, float* peer_n, float* peer_s, int reverse,
              strip_sync sy)
