@@ -10,12 +10,14 @@ CUDA device is usable, calls raise.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 import numpy as np
 
 PKG = Path(__file__).resolve().parent
-LIB_PATH = PKG / "libheat_b200.so"
+# HEAT_B200_LIB selects another build of the same library (the bounds-checked debug twin)
+LIB_PATH = Path(os.environ.get("HEAT_B200_LIB") or PKG / "libheat_b200.so")
 
 OK, E_INVALID, E_CUDA, E_NOMEM, E_STATE, E_PEER, E_TIMEOUT = 0, -1, -2, -3, -4, -5, -6
 F32_FMA, F32_NOFMA, MPI_F64MIX = 0, 1, 2

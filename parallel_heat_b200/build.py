@@ -28,6 +28,21 @@ def stale():
     return any(d.stat().st_mtime > t for d in deps)
 
 
+DEBUG_LIB = PKG / "libheat_b200_dbg.so"
+
+
+def build_debug():
+    """Bounds-checked twin of the library (-DHEAT_BOUNDS_CHECK), for tests/test_bounds_debug.py."""
+    deps = list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cuh")) + list(INCLUDE.glob("*.h"))
+    if DEBUG_LIB.exists() and all(d.stat().st_mtime <= DEBUG_LIB.stat().st_mtime for d in deps):
+        return DEBUG_LIB
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    cmd = [nvcc, *NVCC_FLAGS, "-DHEAT_BOUNDS_CHECK", "-I", str(INCLUDE), "-o", str(DEBUG_LIB), *map(str, sources()),
+           "-ccbin", "/usr/bin/g++"]
+    subprocess.run(cmd, check=True)
+    return DEBUG_LIB
+
+
 def build(force=False, verbose=False):
     """Compile every .cu under csrc/ into libheat_b200.so.  Returns the library path."""
     if not force and not stale():
@@ -46,4 +61,7 @@ def build(force=False, verbose=False):
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if "--debug" in sys.argv:
+        print(build_debug())
+    else:
+        print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -496,6 +496,19 @@ static int enqueue_update(heat_handle* h, bool resid, int fused = 1)
         sy.status = h->d_status;
         sy.timeout_ns = WAIT_TIMEOUT_NS;
     }
+#ifdef HEAT_BOUNDS_CHECK
+    {
+        mem_window w = {};
+        const size_t n = (size_t)h->nloc * h->pitch;
+        w.lo[0] = in, w.hi[0] = in + n;
+        w.lo[1] = out, w.hi[1] = out + n;
+        if (pn) w.lo[2] = pn, w.hi[2] = pn + (size_t)h->ghost * h->pitch;
+        if (ps) w.lo[3] = ps, w.hi[3] = ps + (size_t)h->ghost * h->pitch;
+        // one window for the whole device: the debug build runs one pass at a time
+        CK(cudaDeviceSynchronize());
+        CK(cudaMemcpyToSymbol(g_window, &w, sizeof w));
+    }
+#endif
     const int reverse = h->serpentine ? (int)(h->sweeps & 1) : 0;
     h->sweeps++;
     if (fused > 1) CK(launch_tb(h, fused, in, out, pn, ps, reverse));
@@ -1057,3 +1070,14 @@ extern "C" int heat_step_residual_noalloc(const void* d_in, void* d_out, int nx,
     CK(cudaGetLastError());
     return HEAT_OK;
 }
+
+// ------------------------------------------------------------------ debug build only
+#ifdef HEAT_BOUNDS_CHECK
+// number of out-of-window accesses the update kernels attempted on the current device so far
+extern "C" int heat_debug_violations(unsigned* count)
+{
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpyFromSymbol(count, g_violations, sizeof(unsigned)));
+    return HEAT_OK;
+}
+#endif

@@ -48,8 +48,38 @@ __device__ __forceinline__ float upd(float c, float n, float s, float e, float w
     }
 }
 
+#ifdef HEAT_BOUNDS_CHECK
+// Debug build only (python -m parallel_heat_b200.build --debug -> libheat_b200_dbg.so): every
+// access of the update kernels is checked against the buffer it must stay inside; a violation is
+// counted and the access suppressed.  compute-sanitizer is closed on the GPU pool, this is its
+// stand-in (tests/test_bounds_debug.py).  The host sets the windows before every launch.
+struct mem_window {
+    const float* lo[4]; // in, out, north peer rows, south peer rows
+    const float* hi[4];
+};
+__device__ mem_window g_window;
+__device__ unsigned g_violations;
+__device__ __forceinline__ bool inside(const float* p, int n, int first, int last)
+{
+    for (int k = first; k <= last; k++)
+        if (g_window.lo[k] && p >= g_window.lo[k] && p + n <= g_window.hi[k]) return true;
+    atomicAdd(&g_violations, 1u);
+    return false;
+}
+__device__ __forceinline__ float4 ld4(const float* p)
+{
+    return inside(p, 4, 0, 0) ? *reinterpret_cast<const float4*>(p) : make_float4(0.f, 0.f, 0.f, 0.f);
+}
+__device__ __forceinline__ float ld1(const float* p) { return inside(p, 1, 0, 0) ? *p : 0.0f; }
+__device__ __forceinline__ void st4(float* p, float4 v)
+{
+    if (inside(p, 4, 1, 3)) *reinterpret_cast<float4*>(p) = v;
+}
+#else
 __device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ float ld1(const float* p) { return *p; }
 __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+#endif
 
 // ------------------------------------------------------------------ K0 inidat
 // (float)(ix*(nx-ix-1)*iy*(ny-iy-1)) with the int32 wrap of the reference (M:320).
@@ -253,7 +283,7 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
     float* q = out + (int64_t)r0 * pitch + col;
     float4 n = ld4(p);
     float4 c = ld4(p + pitch);
-    float ec = edge_lane ? p[pitch + edge_off] : 0.0f;
+    float ec = edge_lane ? ld1(p + pitch + edge_off) : 0.0f;
     p += 2 * pitch; // points at row r+1 (the S row of the first output row)
 
     // Almost every warp takes this branch: no ring or padding column among its 128 columns, a full
@@ -269,7 +299,7 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
 #pragma unroll
             for (int u = 0; u < UNROLL; u++) {
                 s[u] = ld4(p + (int64_t)u * pitch);
-                es[u] = el ? p[(int64_t)u * pitch + edge_off] : 0.0f;
+                es[u] = el ? ld1(p + (int64_t)u * pitch + edge_off) : 0.0f;
             }
 #pragma unroll
             for (int u = 0; u < UNROLL; u++) {
@@ -305,7 +335,7 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
             // rows past the tile are clamped to its last S row: loaded but never used for a store
             const int64_t off = (int64_t)min(u, r1 - 1 - r) * pitch;
             s[u] = ld4(p + off);
-            es[u] = edge_lane ? p[off + edge_off] : 0.0f;
+            es[u] = edge_lane ? ld1(p + off + edge_off) : 0.0f;
         }
 #pragma unroll
         for (int u = 0; u < UNROLL; u++) {
