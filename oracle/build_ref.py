@@ -91,6 +91,8 @@ DEFAULT_MPI = [
     (1024, 1024, True, True, "O3"),
     (8192, 8192, False, True, "O3"), (8192, 8192, False, True, "O0"),
     (16384, 16384, True, True, "O3"),
+    # bench.py --impl reference at N GPUs: the weak-scaling grid (8192*N) x 8192
+    (16384, 8192, False, True, "O3"), (32768, 8192, False, True, "O3"), (65536, 8192, False, True, "O3"),
 ]
 DEFAULT_CUDA = [
     # (nx, ny, conv, nofma)

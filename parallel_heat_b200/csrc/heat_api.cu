@@ -192,6 +192,10 @@ struct heat_handle {
     heat_handle* local_nb[2] = {nullptr, nullptr};
     cudaEvent_t ev_done[2] = {nullptr, nullptr}; // recorded after epoch e in ev_done[e & 1]
     bool serpentine = true;
+    // CUDA graphs of GRAPH_PASSES consecutive passes, one per (newest buffer, sweep direction, fused?)
+    cudaGraphExec_t graphs[2][2][2] = {};
+    cudaStream_t capture_stream = nullptr;
+    bool use_graphs = true;
     bool external_halo = false; // the caller moves the ghost rows between updates
     heat_allreduce_max_fn allreduce = nullptr; // joins the residuals of strips in other processes
     void* allreduce_ctx = nullptr;
@@ -253,6 +257,11 @@ extern "C" int heat_destroy(heat_handle* h)
     if (h->ev_resid) cudaEventDestroy(h->ev_resid);
     for (int k = 0; k < 2; k++)
         if (h->ev_done[k]) cudaEventDestroy(h->ev_done[k]);
+    for (auto& a : h->graphs)
+        for (auto& b : a)
+            for (auto& g : b)
+                if (g) cudaGraphExecDestroy(g);
+    if (h->capture_stream) cudaStreamDestroy(h->capture_stream);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     cudaGetLastError();
     delete h;
@@ -323,6 +332,11 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     h->rows_per_tile = env_int("HEAT_ROWS_PER_TILE", 0);
     h->rows_per_tile_tb = env_int("HEAT_ROWS_PER_TILE_TB", 0);
     h->serpentine = env_int("HEAT_SERPENTINE", 1) != 0;
+#ifdef HEAT_BOUNDS_CHECK
+    h->use_graphs = false; // the debug build synchronises around every pass
+#else
+    h->use_graphs = env_int("HEAT_GRAPHS", 1) != 0;
+#endif
     *out = h;
     return HEAT_OK;
 }
@@ -403,12 +417,15 @@ static cudaError_t launch_tb_t(heat_handle* h, const float* in, float* out, floa
         // best R = 48 / 96 / 128-192 / 128-256 rows at 8192^2 / 16384^2 / 32768^2 / 65536^2, i.e. the
         // band of all resident CTAs is about 2400 rows tall whatever the row length.  Modelling the
         // CTAs as rounds of `resident` (R = 168 at 8192^2: one exact round) was 12 % slower.
-        int per_sm = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, heat_step_tb<ARITH, T, WARPS, false>, WARPS * 32, 0) != cudaSuccess ||
-            per_sm < 1) {
+        static int per_sm_cached = 0; // same for every handle of this instantiation
+        if (per_sm_cached < 1 &&
+            (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_cached, heat_step_tb<ARITH, T, WARPS, false>, WARPS * 32, 0) !=
+                 cudaSuccess ||
+             per_sm_cached < 1)) {
             cudaGetLastError();
-            per_sm = 6;
+            per_sm_cached = 6;
         }
+        const int per_sm = per_sm_cached;
         const long long resident = (long long)per_sm * h->sm_count, colblocks = (wcols + WARPS - 1) / WARPS;
         // (multiples of 3: the kernel's row loop is unrolled by 3)
         rpt = (int)((2400 * colblocks / resident + 12) / 24 * 24);
@@ -523,6 +540,47 @@ static int enqueue_update(heat_handle* h, bool resid, int fused = 1)
     return HEAT_OK;
 }
 
+// GRAPH_PASSES consecutive passes as one CUDA graph (captured on a side stream, launched on the
+// handle's stream).  Replaces per-kernel launches where they dominate: the loop of C:204-211 costs
+// one launch per update, 2-4 us each in the reference's own Table 6.
+static const int GRAPH_PASSES = 16;
+
+static int launch_pass_graph(heat_handle* h, int fused)
+{
+    cudaGraphExec_t& exec = h->graphs[h->cur][h->serpentine ? (int)(h->sweeps & 1) : 0][fused > 1 ? 1 : 0];
+    if (!exec) {
+        if (!h->capture_stream) CK(cudaStreamCreateWithFlags(&h->capture_stream, cudaStreamNonBlocking));
+        const cudaStream_t user = h->stream;
+        const long long it0 = h->it, sweeps0 = h->sweeps;
+        const unsigned long long seq0 = h->seq;
+        const int64_t launches0 = h->launches;
+        cudaGraph_t graph = nullptr;
+        h->stream = h->capture_stream;
+        cudaError_t e = cudaStreamBeginCapture(h->capture_stream, cudaStreamCaptureModeRelaxed);
+        int rc = HEAT_OK;
+        if (e == cudaSuccess) {
+            for (int k = 0; k < GRAPH_PASSES && !rc; k++) rc = enqueue_update(h, false, fused);
+            e = cudaStreamEndCapture(h->capture_stream, &graph);
+        }
+        h->stream = user;
+        h->it = it0, h->sweeps = sweeps0, h->seq = seq0, h->launches = launches0; // nothing ran yet
+        if (rc) {
+            if (graph) cudaGraphDestroy(graph);
+            return rc;
+        }
+        if (e != cudaSuccess || !graph) return fail(HEAT_E_CUDA, "stream capture failed: %s", cudaGetErrorString(e));
+        e = cudaGraphInstantiate(&exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (e != cudaSuccess) return fail(HEAT_E_CUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(e));
+    }
+    CK(cudaGraphLaunch(exec, h->stream));
+    h->it += (long long)GRAPH_PASSES * fused;
+    h->sweeps += GRAPH_PASSES;
+    h->seq += GRAPH_PASSES;
+    h->launches += GRAPH_PASSES;
+    return HEAT_OK;
+}
+
 extern "C" int heat_group_enqueue(heat_handle** hs, int n, int updates)
 {
     if (!hs || n < 1 || updates < 0) return fail(HEAT_E_INVALID, "heat_group_enqueue: bad arguments");
@@ -530,6 +588,15 @@ extern "C" int heat_group_enqueue(heat_handle** hs, int n, int updates)
     const int T = hs[0]->p.temporal_block;
     for (int i = 0; i < updates;) {
         const int fused = (T > 1 && updates - i >= T) ? T : 1;
+        // a single strip replays a captured graph of GRAPH_PASSES passes while enough updates are left
+        // (the launch-bound regime of small grids; state is unchanged after an even number of passes)
+        if (n == 1 && hs[0]->p.nranks == 1 && hs[0]->use_graphs && updates - i >= GRAPH_PASSES * fused) {
+            CK(cudaSetDevice(hs[0]->p.device));
+            int rc = launch_pass_graph(hs[0], fused);
+            if (rc) return rc;
+            i += GRAPH_PASSES * fused;
+            continue;
+        }
         for (int k = 0; k < n; k++) {
             CK(cudaSetDevice(hs[k]->p.device));
             int rc = enqueue_update(hs[k], false, fused);
@@ -580,6 +647,11 @@ extern "C" int heat_group_run(heat_handle** hs, int n, int steps, int* updates_d
         CK(cudaEventRecord(hs[k]->ev0, hs[k]->stream));
     }
     const int T = h0->p.temporal_block;
+    if (K == 0 && total > 0) { // no convergence check: nothing for the host to decide until the end
+        int rc = heat_group_enqueue(hs, n, (int)total);
+        if (rc) return rc;
+        done = total;
+    }
     while (done < total && !conv) {
         // is update number `it` one whose result is checked?
         const bool check = K > 0 && (h0->p.conv_phase == HEAT_PHASE_CUDA ? (h0->it % K == 0) : ((h0->it + 1) % K == 0));

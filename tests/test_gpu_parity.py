@@ -358,3 +358,53 @@ def test_16384_with_convergence_check(ph, oracle):
     want, wdone, wconv = oracle.solve(oracle.inidat(n, n), 41, arith=0, conv_every=20, conv_phase=1)
     assert wdone == 41 and not wconv
     assert_same_bits(got, want, "16384^2")
+
+
+# ---------------------------------------------------------------- parameters and handle API
+@pytest.mark.parametrize("arith", MODES)
+@pytest.mark.parametrize("T", [1, 4])
+def test_anisotropic_coefficients(ph, oracle, arith, T):
+    # cx weights the row+-1 difference, cy the column+-1 difference (M:168-174): with cx != cy a swap shows
+    u = field((70, 260), seed=21)
+    for cx, cy in [(0.05, 0.2), (0.2, 0.05), (0.0, 0.25), (0.125, 0.0)]:
+        want, _, _ = oracle.solve(u, 9, arith=arith, cx=cx, cy=cy)
+        got, _, _ = ph.solve(u, 9, arith=arith, cx=cx, cy=cy, temporal_block=T)
+        assert_same_bits(got, want, f"cx={cx} cy={cy} arith={arith} T={T}")
+
+
+def test_upload_device_set_stream_and_views(ph, oracle):
+    import torch
+    u = field((96, 200), seed=4)
+    d = torch.from_numpy(u).cuda()
+    st = torch.cuda.Stream()
+    with ph.HeatSolver(96, 200, arith=ph.F32_NOFMA) as s:
+        s.set_stream(st.cuda_stream)
+        s.upload_device(d.data_ptr())
+        s.enqueue(5)
+        s.sync()
+        assert s.launch_count() == 5
+        ptr, pitch, rows, first = s.device_view(0)
+        assert (pitch, rows, first) == (224, 96, 0) and ptr  # rows padded to 32 floats
+        got = s.download()
+        assert_same_bits(got, oracle.solve(u, 5, arith=1)[0])
+        done, conv = s.run(0)
+        assert (done, conv) == (0, False) and s.elapsed_ms() >= 0.0
+
+
+def test_strip_errors(ph):
+    with ph.HeatSolver(64, 64, rank=0, nranks=2) as a, ph.HeatSolver(64, 64, rank=1, nranks=2) as b:
+        with pytest.raises(ph.HeatError) as ei:
+            a.connect_local(None, None)  # strip 0 of 2 needs a south neighbour
+        assert ei.value.code == ph.api.E_PEER
+        with pytest.raises(ph.HeatError):
+            a.connect_local(None, a)     # not adjacent
+        a.connect_local(None, b)
+        b.connect_local(a, None)
+        a.upload(ph.inidat(64, 64))
+        b.upload(ph.inidat(64, 64))
+        with pytest.raises(ph.HeatError) as ei:
+            a.run(3)                     # locally connected strips are driven together
+        assert ei.value.code == ph.api.E_STATE
+        assert ph.group_run([a, b], 3) == (3, False)
+    with pytest.raises(ph.HeatError):
+        ph.HeatSolver(6, 64, rank=0, nranks=2, temporal_block=4)  # 3 rows per strip cannot carry 4 ghost rows
