@@ -383,7 +383,10 @@ static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, fl
 {
     const int rows = h->upd_hi - h->upd_lo, ny = h->p.ny;
     if (rows < 1 || ny < 3) return cudaSuccess; // no interior: nothing to update (ring only)
-    constexpr int THREADS = 128, UNROLL = 4;
+#ifndef HEAT_K1_THREADS
+#define HEAT_K1_THREADS 128
+#endif
+    constexpr int THREADS = HEAT_K1_THREADS, UNROLL = 4;
     int rpt = pick_rows_per_tile(h, THREADS);
     if (rpt < h->ghost) rpt = h->ghost;
     if ((rows + rpt - 1) / rpt > 65535) rpt = (rows + 65534) / 65535; // grid.y limit: taller tiles
@@ -407,7 +410,10 @@ static cudaError_t launch_tb_t(heat_handle* h, const float* in, float* out, floa
 {
     const int rows = h->upd_hi - h->upd_lo, ny = h->p.ny;
     if (rows < 1 || ny < 3) return cudaSuccess;
-    constexpr int WARPS = 4;
+#ifndef HEAT_TB_WARPS
+#define HEAT_TB_WARPS 1 // warps per CTA of the temporal-blocking kernel: 1 beat 2 and 4 by 3-5 % (finer balance)
+#endif
+    constexpr int WARPS = HEAT_TB_WARPS;
     const int64_t wcols = (h->pitch + 119) / 120;
     int rpt = h->rows_per_tile_tb;
     if (rpt <= 0) {

@@ -12,5 +12,5 @@ dump() { # $1 = substring of the mangled name, $2 = output
 }
 dump "heat_step_vecILi0ELb0ELi128ELi4ELb0" profiles/sass_heat_step_vec_fma.txt
 dump "heat_step_vecILi0ELb1ELi128ELi4ELb0" profiles/sass_heat_step_vec_fma_residual.txt
-dump "heat_step_tbILi0ELi4ELi4ELb0" profiles/sass_heat_step_tb_fma_T4.txt
+dump "heat_step_tbILi0ELi4ELi1ELb0" profiles/sass_heat_step_tb_fma_T4.txt
 grep -cE "UTMALDG|UBLKCP|LDG.E.128|STG.E.128|SHFL|REDUX" profiles/sass_heat_step_vec_fma_residual.txt || true
