@@ -113,6 +113,11 @@ int heat_elapsed_ms(heat_handle *h, float *ms);
 int heat_residual(heat_handle *h, float *residual);
 /* Newest field -> host; a strip writes only the rows it owns into full_grid. */
 int heat_download(heat_handle *h, float *full_grid);
+/* The same for a rank that holds only its strip: local_rows = the strip's window, dense
+ * local_rows x ny (global rows first_global_row ..., ghost rows included: see heat_device_view);
+ * own_rows receives the rows the strip owns (heat_strip_rows), dense. */
+int heat_upload_local(heat_handle *h, const float *local_rows);
+int heat_download_local(heat_handle *h, float *own_rows);
 /* Device pointer / pitch (in floats) / local row count of the newest (which=0) or older
  * (which=1) buffer, and the global row of local row 0. */
 int heat_device_view(heat_handle *h, int which, void **d_ptr, int64_t *pitch, int *local_rows, int *first_global_row);

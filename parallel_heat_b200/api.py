@@ -70,6 +70,8 @@ SIGNATURES = {
     "heat_elapsed_ms": (C.c_int, [_H, _fp]),
     "heat_residual": (C.c_int, [_H, _fp]),
     "heat_download": (C.c_int, [_H, _fp]),
+    "heat_upload_local": (C.c_int, [_H, _fp]),
+    "heat_download_local": (C.c_int, [_H, _fp]),
     "heat_device_view": (C.c_int, [_H, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), _ip, _ip]),
     "heat_launch_count": (C.c_int, [_H, C.POINTER(C.c_int64)]),
     "heat_step_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, C.c_void_p]),
@@ -218,6 +220,17 @@ class HeatSolver:
             out = np.zeros((self.params.nx, self.params.ny), np.float32)
         assert out.dtype == np.float32 and out.flags.c_contiguous
         _check(load().heat_download(self._h, out.ctypes.data_as(_fp)))
+        return out
+
+    def upload_local(self, local_rows):
+        """local_rows: this strip's window (device_view()[2] rows from global row device_view()[3]), dense."""
+        g, p = _f32(local_rows)
+        _check(load().heat_upload_local(self._h, p))
+
+    def download_local(self, out):
+        """out: (rows this strip owns, ny) float32, C-contiguous."""
+        assert out.dtype == np.float32 and out.flags.c_contiguous
+        _check(load().heat_download_local(self._h, out.ctypes.data_as(_fp)))
         return out
 
     def device_view(self, which=0):

@@ -824,6 +824,26 @@ extern "C" int heat_download(heat_handle* h, float* full_grid)
     return HEAT_OK;
 }
 
+// A strip's own window only: what a rank that never holds the full field passes in / gets back.
+extern "C" int heat_upload_local(heat_handle* h, const float* local_rows)
+{
+    if (!h || !local_rows) return fail(HEAT_E_INVALID, "heat_upload_local: bad arguments");
+    // same copy as heat_upload, whose source starts at the strip's first local row
+    return upload_from(h, local_rows - (size_t)h->lo * h->p.ny, cudaMemcpyHostToDevice);
+}
+
+extern "C" int heat_download_local(heat_handle* h, float* own_rows)
+{
+    if (!h || !own_rows) return fail(HEAT_E_INVALID, "heat_download_local: bad arguments");
+    CK(cudaSetDevice(h->p.device));
+    const int first = h->row0 - h->lo;
+    CK(cudaMemcpy2DAsync(own_rows, (size_t)h->p.ny * sizeof(float), h->buf[h->cur] + (size_t)first * h->pitch,
+                         h->pitch * sizeof(float), (size_t)h->p.ny * sizeof(float), h->rows_own, cudaMemcpyDeviceToHost,
+                         h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return HEAT_OK;
+}
+
 extern "C" int heat_device_view(heat_handle* h, int which, void** d_ptr, int64_t* pitch, int* local_rows, int* first_global_row)
 {
     if (!h || (which != 0 && which != 1)) return fail(HEAT_E_INVALID, "heat_device_view: bad arguments");

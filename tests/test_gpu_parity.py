@@ -408,3 +408,25 @@ def test_strip_errors(ph):
         assert ph.group_run([a, b], 3) == (3, False)
     with pytest.raises(ph.HeatError):
         ph.HeatSolver(6, 64, rank=0, nranks=2, temporal_block=4)  # 3 rows per strip cannot carry 4 ghost rows
+
+
+def test_upload_and_download_of_a_strip_window(ph, oracle):
+    # a rank that holds only its own window (ghost rows included) of the field
+    u = field((90, 140), seed=8)
+    g = 3
+    ss = [ph.HeatSolver(90, 140, rank=r, nranks=g, arith=ph.F32_NOFMA, temporal_block=2) for r in range(g)]
+    try:
+        for r, s in enumerate(ss):
+            s.connect_local(ss[r - 1] if r > 0 else None, ss[r + 1] if r < g - 1 else None)
+        for s in ss:
+            _, _, nloc, lo = s.device_view(0)
+            s.upload_local(np.ascontiguousarray(u[lo:lo + nloc]))
+        ph.group_run(ss, 7)
+        out = np.zeros_like(u)
+        for r, s in enumerate(ss):
+            r0, n = ph.strip_rows(90, g, r)
+            s.download_local(out[r0:r0 + n])
+    finally:
+        for s in ss:
+            s.close()
+    assert_same_bits(out, oracle.solve(u, 7, arith=1)[0])
