@@ -73,6 +73,14 @@ def ncu_traffic(name):
     return None
 
 
+def host_cores():
+    """Cores this process may use (what `nproc` prints)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 class ClockSampler:
     """nvidia-smi clocks/throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
 
@@ -128,9 +136,10 @@ class ClockSampler:
 def run_reference_arm(args, wl, rank, world):
     if rank != 0:
         return
+    cores = host_cores()
+    os.environ["OMP_NUM_THREADS"] = str(cores)  # torchrun exports OMP_NUM_THREADS=1 to its workers
     from oracle import pyoracle as O
     nx, ny = wl["nx"], wl["ny"]
-    cores = os.cpu_count() or 1
     out = {"metric": METRIC, "unit": "GLUP/s", "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
            "warmup": args.warmup, "higher_is_better": True, "scaling": wl["scaling"], "vs_baseline": None,
            "dtype": "f32 grid, f64-mixed arithmetic (M:168-174)", "data": "synthetic",
@@ -139,10 +148,10 @@ def run_reference_arm(args, wl, rank, world):
     lups_per_update = (nx - 2) * (ny - 2)
     if exe.exists():
         # bounded sample: a short probe sizes the run to about 20 s of loop time
-        probe = O.run_reference("mpi", nx, ny, 2, conv=wl["conv_every"] > 0, omp=True, opt="O3", capture=False)
+        probe = O.run_reference("mpi", nx, ny, 2, conv=wl["conv_every"] > 0, omp=True, opt="O3", capture=False, threads=cores)
         per_update = max(probe["loop_secs"] / 3, 1e-6)
         updates = int(max(3, min(args.steps + args.warmup, 20.0 / per_update)))
-        r = O.run_reference("mpi", nx, ny, updates - 1, conv=wl["conv_every"] > 0, omp=True, opt="O3", capture=False)
+        r = O.run_reference("mpi", nx, ny, updates - 1, conv=wl["conv_every"] > 0, omp=True, opt="O3", capture=False, threads=cores)
         secs, kind = r["loop_secs"], "reference"
         sample = (f"{updates} updates of {nx}x{ny}: unmodified mpi_heat_improved_persistent_stat.c, -O3 -fopenmp -DOMPCH, "
                   f"{cores} OpenMP threads, 1-rank MPI stand-in, loop-only time (M:159-265)")
@@ -166,16 +175,17 @@ def run_reference_arm(args, wl, rank, world):
 
 # ------------------------------------------------------------------------------------ cpu baseline (rank 0, N=1)
 def cpu_baseline(wl):
+    cores = host_cores()
+    os.environ["OMP_NUM_THREADS"] = str(cores)
     from oracle import pyoracle as O
     nx, ny = wl["nx"], wl["ny"]
-    cores = os.cpu_count() or 1
     lups = (nx - 2) * (ny - 2)
     exe = O.ref_binary("mpi", nx, ny, conv=wl["conv_every"] > 0, omp=True, opt="O3")
     try:
         if exe.exists():
-            probe = O.run_reference("mpi", nx, ny, 2, conv=wl["conv_every"] > 0, omp=True, opt="O3", capture=False)
+            probe = O.run_reference("mpi", nx, ny, 2, conv=wl["conv_every"] > 0, omp=True, opt="O3", capture=False, threads=cores)
             updates = int(max(3, min(2000, 15.0 / max(probe["loop_secs"] / 3, 1e-6))))
-            r = O.run_reference("mpi", nx, ny, updates - 1, conv=wl["conv_every"] > 0, omp=True, opt="O3", capture=False)
+            r = O.run_reference("mpi", nx, ny, updates - 1, conv=wl["conv_every"] > 0, omp=True, opt="O3", capture=False, threads=cores)
             return {"value": lups * updates / r["loop_secs"] / 1e9, "unit": "GLUP/s", "cores": cores, "kind": "reference",
                     "sample": f"{updates} updates of {nx}x{ny}, unmodified reference MPI source -O3 -fopenmp -DOMPCH, "
                               f"{cores} threads, loop-only"}
