@@ -430,3 +430,18 @@ def test_upload_and_download_of_a_strip_window(ph, oracle):
         for s in ss:
             s.close()
     assert_same_bits(out, oracle.solve(u, 7, arith=1)[0])
+
+
+@pytest.mark.parametrize("arith", MODES)
+@pytest.mark.parametrize("T", [1, 4])
+def test_denormals_zeros_and_huge_values(ph, oracle, arith, T):
+    # denormals are kept (no flush to zero), exact zeros and values near FLT_MAX/4 behave like on the CPU
+    rng = np.random.default_rng(12)
+    u = (rng.standard_normal((40, 140)) * 1e-41).astype(np.float32)        # all denormal
+    u[5:9, 20:60] = 0.0
+    u[20:24, :] = (rng.standard_normal((4, 140)) * 1e-37).astype(np.float32)  # around the smallest normals
+    u[30:34, 10:130] = (rng.standard_normal((4, 120)) * 2e37).astype(np.float32)
+    assert np.isfinite(u).all()
+    want, _, _ = oracle.solve(u, 9, arith=arith)
+    got, _, _ = ph.solve(u, 9, arith=arith, temporal_block=T)
+    assert_same_bits(got, want, f"denormals arith={arith} T={T}")
