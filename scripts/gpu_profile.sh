@@ -1,11 +1,14 @@
 #!/bin/bash
-# GPU tests + ncu launch list + one full capture of the update kernel (1 GPU).
-set -x
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
-CMD="python bench.py --steps 20 --warmup 3 --no-e2e --no-cpu-baseline"
+python bench.py --impl reference > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err
+python bench.py > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err
+tail -c 400 gpurun_out/bench_default.json
+CMD="python bench.py --steps 40 --warmup 4 --no-e2e --no-cpu-baseline --no-also"
 $CMD > gpurun_out/plain.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
+ncu --metrics gpu__time_duration.sum --clock-control none -c 80 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
 $CMD > gpurun_out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:heat_step_vec -s 10 -c 3 -f -o gpurun_out/prof_step $CMD > gpurun_out/ncu_full.log 2>&1
-tail -3 gpurun_out/pytest_gpu.log gpurun_out/plain.log gpurun_out/ncu_launches.log gpurun_out/ncu_full.log
+ncu --set full --clock-control none --import-source on -k regex:heat_step_vec -s 20 -c 4 -f -o gpurun_out/prof_k1 $CMD > gpurun_out/ncu_k1.log 2>&1
+CMD4="python bench.py --steps 64 --warmup 16 --temporal-block 4 --no-e2e --no-cpu-baseline --no-also"
+$CMD4 > gpurun_out/plain4.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:heat_step_tb -s 6 -c 4 -f -o gpurun_out/prof_k4 $CMD4 > gpurun_out/ncu_k4.log 2>&1
+ls -la gpurun_out/*.ncu-rep
