@@ -84,6 +84,8 @@ class StripSolver:
         if self.halo == "p2p":
             self._connect_p2p()
         elif self.halo == "sendrecv":
+            if int(self.solver.params.temporal_block) > 1:
+                raise ValueError("halo='sendrecv' moves one ghost row per update: use temporal_block=1 (or halo='p2p')")
             self.solver.set_halo_mode(api.HALO_EXTERNAL)
             if solver_cls is None:
                 # NCCL P2P ops are ordered against torch's current stream: run the updates there too

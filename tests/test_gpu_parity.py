@@ -445,3 +445,36 @@ def test_denormals_zeros_and_huge_values(ph, oracle, arith, T):
     want, _, _ = oracle.solve(u, 9, arith=arith)
     got, _, _ = ph.solve(u, 9, arith=arith, temporal_block=T)
     assert_same_bits(got, want, f"denormals arith={arith} T={T}")
+
+
+@pytest.mark.parametrize("T", [1, 4])
+def test_65536_square_band_matches_oracle(ph, oracle, T):
+    # BASELINE config 4's grid: 2^32 points, so every index past row 32768 needs 64-bit arithmetic (the
+    # reference cannot run this size at all, C:170).  After k updates a row depends only on the k rows
+    # above and below it, so a band of rows can be checked against the oracle run on that band alone.
+    import torch
+    free, _ = torch.cuda.mem_get_info()
+    if free < 36 * 2**30:
+        pytest.skip("needs 36 GiB of free device memory")
+    n, k = 65536, 8
+    with ph.HeatSolver(n, n, arith=ph.F32_FMA, temporal_block=T) as s:
+        s.init_inidat()
+        s.run(k)
+        ptr, pitch, rows, first = s.device_view(0)
+        assert (pitch, rows, first) == (n, n, 0)
+        for lo in (0, 40000, n - 40):  # top edge, beyond the 2^31-element mark, bottom edge
+            band = 40
+
+            class _Arr:
+                pass
+            a = _Arr()
+            a.__cuda_array_interface__ = {"shape": (band, n), "typestr": "<f4", "version": 3,
+                                          "data": (ptr + 4 * pitch * lo, False)}
+            got = torch.as_tensor(a, device="cuda").cpu().numpy()
+            ix = np.arange(lo, lo + band, dtype=np.uint32)[:, None]
+            iy = np.arange(n, dtype=np.uint32)[None, :]
+            ini = (ix * (np.uint32(n) - ix - np.uint32(1)) * iy * (np.uint32(n) - iy - np.uint32(1))).view(np.int32).astype(np.float32)
+            want, _, _ = oracle.solve(ini, k, arith=0)
+            top = 0 if lo == 0 else k                    # rows nearer than k to a cut edge of the band are not comparable
+            bot = band if lo + band == n else band - k
+            assert_same_bits(got[top:bot], want[top:bot], f"65536^2 T={T} rows {lo + top}..{lo + bot}")
