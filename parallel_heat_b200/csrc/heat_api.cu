@@ -652,28 +652,24 @@ extern "C" int heat_group_run(heat_handle** hs, int n, int steps, int* updates_d
         CK(cudaSetDevice(hs[k]->p.device));
         CK(cudaEventRecord(hs[k]->ev0, hs[k]->stream));
     }
-    const int T = h0->p.temporal_block;
-    if (K == 0 && total > 0) { // no convergence check: nothing for the host to decide until the end
-        int rc = heat_group_enqueue(hs, n, (int)total);
-        if (rc) return rc;
-        done = total;
-    }
     while (done < total && !conv) {
-        // is update number `it` one whose result is checked?
-        const bool check = K > 0 && (h0->p.conv_phase == HEAT_PHASE_CUDA ? (h0->it % K == 0) : ((h0->it + 1) % K == 0));
-        // T updates can be fused when none of them is a checked one and T are left
-        int fused = 1;
-        if (T > 1 && !check && total - done >= T) {
-            long long to_check = T; // updates from now until the next checked one
-            if (K > 0) {
-                const long long ph = h0->p.conv_phase == HEAT_PHASE_CUDA ? h0->it % K : (h0->it + 1) % K;
-                to_check = (K - ph) % K;
-            }
-            if (to_check >= T) fused = T;
+        // how many plain updates come before the next checked one?
+        long long plain = total - done;
+        if (K > 0) {
+            const long long ph = h0->p.conv_phase == HEAT_PHASE_CUDA ? h0->it % K : (h0->it + 1) % K;
+            plain = (K - ph) % K; // 0: update number `it` is itself a checked one
+            if (plain > total - done) plain = total - done;
         }
+        if (plain > 0) { // fused passes and graphs are chosen inside; nothing for the host to decide
+            int rc = heat_group_enqueue(hs, n, (int)plain);
+            if (rc) return rc;
+            done += plain;
+            continue;
+        }
+        const bool check = true;
         for (int k = 0; k < n; k++) {
             CK(cudaSetDevice(hs[k]->p.device));
-            int rc = enqueue_update(hs[k], check, fused);
+            int rc = enqueue_update(hs[k], check, 1);
             if (rc) return rc;
             if (check) {
                 // one 4-byte read-back per K updates: the only host sync in the loop
@@ -681,7 +677,7 @@ extern "C" int heat_group_run(heat_handle** hs, int n, int steps, int* updates_d
                 CK(cudaEventRecord(hs[k]->ev_resid, hs[k]->stream));
             }
         }
-        done += fused;
+        done += 1;
         if (check) {
             float r = 0.0f;
             for (int k = 0; k < n; k++) {

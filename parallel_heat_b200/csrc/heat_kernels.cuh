@@ -489,14 +489,18 @@ heat_step_tb(const float* __restrict__ in, float* __restrict__ out, int nrows, i
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int npitch = (int)pitch;
-    const int wcol = blockIdx.x * WARPS + (threadIdx.x >> 5);
+    // The warps that hold a ring column (first and last warp column) and the first/last row tiles
+    // take the generic path, about twice as slow: they are handed out first, so that they are not
+    // what the end of the pass waits for.
+    const int nwcol = gridDim.x * WARPS, wlin = blockIdx.x * WARPS + (threadIdx.x >> 5);
+    const int wcol = (WARPS == 1 && nwcol > 2) ? (wlin == 0 ? 0 : wlin == 1 ? nwcol - 1 : wlin - 1) : wlin;
     const int c0 = wcol * 120 - 4;
     const int col = c0 + lane * 4;
     const bool inrange = col >= 0 && col < npitch;
     const bool stores = inrange && lane >= 1 && lane <= 30;
 
     const int ntiles = gridDim.y;
-    const int tile = tile_of_block<SYNC>((int)blockIdx.y, ntiles, reverse);
+    const int tile = tile_of_block<true>((int)blockIdx.y, ntiles, reverse); // edge tiles first, always
     const int r0 = row_lo + tile * rows_per_tile;
     const int r1 = min(r0 + rows_per_tile, row_hi);
     const bool edge_n = r0 < row_lo + T, edge_s = r1 > row_hi - T;
