@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 N=$(nvidia-smi -L | wc -l)
 TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
-timeout 200 $TR --nproc-per-node $N --master-port 29501 scripts/check_strips.py > gpurun_out/check_strips.log 2>&1; echo "rc=$?" >> gpurun_out/check_strips.log
+timeout 200 $TR --nproc-per-node $N --master-port 29501 tests/check_strips_torchrun.py > gpurun_out/check_strips.log 2>&1; echo "rc=$?" >> gpurun_out/check_strips.log
 tail -5 gpurun_out/check_strips.log
 : > gpurun_out/n8.log
 run() { echo "## $1" >> gpurun_out/n8.log; shift; timeout 240 "$@" >> gpurun_out/n8.log 2>&1; }

@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """Under torchrun: row strips on every GPU of the box against the undecomposed CPU oracle (bit-exact).
-    python -m torch.distributed.run --nproc-per-node N scripts/check_strips.py"""
+    python -m torch.distributed.run --nproc-per-node N tests/check_strips_torchrun.py"""
 import os
 import sys
 from pathlib import Path

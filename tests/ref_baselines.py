@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """Reported baselines: the reference's own programs on this box.
-Run on the GPU box:  python scripts/ref_baselines.py > gpurun_out/ref_baselines.json
+Run on the GPU box:  python tests/ref_baselines.py > gpurun_out/ref_baselines.json
 Loop-only time: MPI program = the stand-in's loop stamps; CUDA program = wall(STEPS=S) - wall(STEPS=0),
 because its own timer stops without a device sync (cuda_heat.cu:239)."""
 import json
