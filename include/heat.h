@@ -85,6 +85,11 @@ int heat_readdat_bin(const char *fnam, int *nx, int *ny, float *u, size_t capaci
  * executed; the reference programs print updates_done-1 when they converge (M:302, C:256). */
 int heat_solve(const heat_params *p, float *grid, int *updates_done, int *converged);
 
+/* The same over the first `ngpus` devices of this process: one row strip per GPU, ghost rows moved by
+ * peer stores over NVLink, one host thread.  Replaces M:51-297 (topology, scatter, halo requests, loop,
+ * gather) inside one box.  p->rank/nranks/device are ignored. */
+int heat_solve_gpus(const heat_params *p, int ngpus, float *grid, int *updates_done, int *converged);
+
 /* ---- device-resident handle (what C keeps alive in dvc_grids[2], C:177-198) ---------- */
 int heat_create(const heat_params *p, heat_handle **out);
 int heat_destroy(heat_handle *h);

@@ -7,10 +7,10 @@ build.py  in-tree nvcc build of libheat_b200.so
 """
 from .api import (F32_FMA, F32_NOFMA, MPI_F64MIX, PHASE_CUDA, PHASE_MPI, STEPS_CUDA, STEPS_MPI,  # noqa: F401
                   HeatError, HeatParams, HeatSolver, default_params, device_count, group_enqueue, group_run,
-                  inidat, load, prtdat, prtdat_bin, readdat_bin, solve, step_device, step_residual_device,
+                  inidat, load, prtdat, prtdat_bin, readdat_bin, solve, solve_gpus, step_device, step_residual_device,
                   strip_rows)
 
-__all__ = ["HeatSolver", "HeatParams", "HeatError", "solve", "inidat", "prtdat", "prtdat_bin", "readdat_bin",
+__all__ = ["HeatSolver", "HeatParams", "HeatError", "solve", "solve_gpus", "inidat", "prtdat", "prtdat_bin", "readdat_bin",
            "strip_rows", "default_params", "device_count", "load", "group_run", "group_enqueue",
            "step_device", "step_residual_device",
            "F32_FMA", "F32_NOFMA", "MPI_F64MIX", "STEPS_CUDA", "STEPS_MPI", "PHASE_CUDA", "PHASE_MPI"]

@@ -58,6 +58,7 @@ SIGNATURES = {
     "heat_prtdat_bin": (C.c_int, [C.c_int, C.c_int, _fp, C.c_char_p]),
     "heat_readdat_bin": (C.c_int, [C.c_char_p, _ip, _ip, _fp, C.c_size_t]),
     "heat_solve": (C.c_int, [C.POINTER(HeatParams), _fp, _ip, _ip]),
+    "heat_solve_gpus": (C.c_int, [C.POINTER(HeatParams), C.c_int, _fp, _ip, _ip]),
     "heat_create": (C.c_int, [C.POINTER(HeatParams), C.POINTER(_H)]),
     "heat_destroy": (C.c_int, [_H]),
     "heat_set_stream": (C.c_int, [_H, C.c_void_p]),
@@ -169,6 +170,15 @@ def solve(grid, steps, **params):
     p = default_params(nx=g.shape[0], ny=g.shape[1], steps=steps, **params)
     done, conv = C.c_int(0), C.c_int(0)
     _check(load().heat_solve(C.byref(p), g.ctypes.data_as(_fp), C.byref(done), C.byref(conv)))
+    return g, done.value, bool(conv.value)
+
+
+def solve_gpus(grid, steps, ngpus, **params):
+    """heat_solve_gpus(): one row strip per GPU of this process.  Returns (field, updates_done, converged)."""
+    g = np.array(grid, dtype=np.float32, order="C", copy=True)
+    p = default_params(nx=g.shape[0], ny=g.shape[1], steps=steps, **params)
+    done, conv = C.c_int(0), C.c_int(0)
+    _check(load().heat_solve_gpus(C.byref(p), ngpus, g.ctypes.data_as(_fp), C.byref(done), C.byref(conv)))
     return g, done.value, bool(conv.value)
 
 

@@ -880,6 +880,32 @@ extern "C" int heat_solve(const heat_params* p, float* grid, int* updates_done, 
     return rc;
 }
 
+// One-shot over the first `ngpus` devices of this process: G row strips, one per GPU, one host thread
+// (what src/heat_main.c --gpus G does).  Replaces the whole of M:51-297 for a single box.
+extern "C" int heat_solve_gpus(const heat_params* p, int ngpus, float* grid, int* updates_done, int* converged)
+{
+    if (!p || !grid || ngpus < 1 || ngpus > 64) return fail(HEAT_E_INVALID, "heat_solve_gpus: bad arguments");
+    if (ngpus == 1) return heat_solve(p, grid, updates_done, converged);
+    heat_handle* h[64] = {};
+    heat_params q = *p;
+    q.nranks = ngpus;
+    int rc = HEAT_OK;
+    for (int r = 0; r < ngpus && !rc; r++) {
+        q.rank = r;
+        q.device = r;
+        rc = heat_create(&q, &h[r]);
+    }
+    for (int r = 0; r < ngpus && !rc; r++) rc = heat_connect_local(h[r], r > 0 ? h[r - 1] : nullptr, r < ngpus - 1 ? h[r + 1] : nullptr);
+    for (int r = 0; r < ngpus && !rc; r++) rc = heat_upload(h[r], grid);
+    if (!rc) rc = heat_group_run(h, ngpus, p->steps, updates_done, converged);
+    for (int r = 0; r < ngpus && !rc; r++) rc = heat_download(h[r], grid);
+    char keep[sizeof g_err];
+    memcpy(keep, g_err, sizeof keep); // heat_destroy must not hide the first error
+    for (int r = 0; r < ngpus; r++) heat_destroy(h[r]);
+    if (rc) memcpy(g_err, keep, sizeof keep);
+    return rc;
+}
+
 // ------------------------------------------------------------------ stateless updates (C:140-163, C:42-138)
 template <bool RESID>
 static int step_device(const void* d_in, void* d_out, int nx, int ny, float cx, float cy, int arith, unsigned* resid, void* stream)

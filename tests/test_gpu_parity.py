@@ -478,3 +478,12 @@ def test_65536_square_band_matches_oracle(ph, oracle, T):
             top = 0 if lo == 0 else k                    # rows nearer than k to a cut edge of the band are not comparable
             bot = band if lo + band == n else band - k
             assert_same_bits(got[top:bot], want[top:bot], f"65536^2 T={T} rows {lo + top}..{lo + bot}")
+
+
+def test_solve_gpus_with_one_gpu_is_heat_solve(ph, oracle):
+    u = ph.inidat(64, 96)
+    got, done, _ = ph.solve_gpus(u, 12, 1, arith=ph.F32_NOFMA)
+    assert done == 12
+    assert_same_bits(got, oracle.solve(u, 12, arith=1)[0])
+    with pytest.raises(ph.HeatError):
+        ph.solve_gpus(u, 12, 0)

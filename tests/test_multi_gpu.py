@@ -93,3 +93,13 @@ def test_one_process_two_gpus(ph, oracle):
             s.close()
     want, _, _ = oracle.solve(u, 60, arith=1)
     assert done == 60 and np.array_equal(out.view(np.uint32), want.view(np.uint32))
+
+
+@needs2
+def test_solve_gpus_one_shot(ph, oracle):
+    u = ph.inidat(400, 300)
+    want, wdone, wconv = oracle.solve(u, 61, arith=2, conv_every=20, conv_phase=0, step_convention=1)
+    got, done, conv = ph.solve_gpus(u, 61, min(ngpus(), 4), arith=ph.MPI_F64MIX, conv_every=20, conv_phase=ph.PHASE_MPI,
+                                    step_convention=ph.STEPS_MPI, temporal_block=2)
+    assert (done, conv) == (wdone, wconv)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
