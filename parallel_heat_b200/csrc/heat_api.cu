@@ -196,6 +196,13 @@ struct heat_handle {
     cudaGraphExec_t graphs[2][2][2] = {};
     cudaStream_t capture_stream = nullptr;
     bool use_graphs = true;
+    // K5: the whole field resident in shared memory across many updates (small grids)
+    bool use_resident = true;
+    float* res_halo = nullptr;
+    unsigned long long* res_flags = nullptr;
+    unsigned long long res_epoch = 0;
+    int res_ctas = 0, res_threads = 0, res_tpr = 0, res_ghost = 1;
+    size_t res_smem = 0;
     bool external_halo = false; // the caller moves the ghost rows between updates
     heat_allreduce_max_fn allreduce = nullptr; // joins the residuals of strips in other processes
     void* allreduce_ctx = nullptr;
@@ -250,6 +257,8 @@ extern "C" int heat_destroy(heat_handle* h)
     if (h->flags) cudaFree(h->flags);
     if (h->d_resid) cudaFree(h->d_resid);
     if (h->d_edge_count) cudaFree(h->d_edge_count);
+    if (h->res_halo) cudaFree(h->res_halo);
+    if (h->res_flags) cudaFree(h->res_flags);
     if (h->h_resid) cudaFreeHost(h->h_resid);
     if (h->h_status) cudaFreeHost(h->h_status);
     if (h->ev0) cudaEventDestroy(h->ev0);
@@ -334,8 +343,10 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     h->serpentine = env_int("HEAT_SERPENTINE", 1) != 0;
 #ifdef HEAT_BOUNDS_CHECK
     h->use_graphs = false; // the debug build synchronises around every pass
+    h->use_resident = false;
 #else
     h->use_graphs = env_int("HEAT_GRAPHS", 1) != 0;
+    h->use_resident = env_int("HEAT_RESIDENT", 1) != 0;
 #endif
     *out = h;
     return HEAT_OK;
@@ -546,6 +557,99 @@ static int enqueue_update(heat_handle* h, bool resid, int fused = 1)
     return HEAT_OK;
 }
 
+// ---- K5: many updates in one cooperative launch, field resident in shared memory
+static const int RESIDENT_MIN_UPDATES = 4;
+
+template <int ARITH>
+static int resident_prepare_t(heat_handle* h)
+{
+    // one CTA per SM at most; every band at least G rows tall so that a ghost zone never reaches past a neighbour
+    const int interior = h->nloc - 2;
+    int G = env_int("HEAT_RESIDENT_G", 6); // measured at 1024^2: G=1 203, 2 313, 4 412, 6 439, 8 415 GLUP/s
+    if (G < 1) G = 1;
+    if (G > 16) G = 16;
+    int ctas = interior / G;
+    if (ctas > h->sm_count) ctas = h->sm_count;
+    if (ctas < 1) ctas = 1;
+    if (interior / ctas < G) G = interior / ctas; // a single short band
+    const int ncg = (int)(h->pitch / 4);
+    int tpr = (ncg + 31) / 32 * 32;
+    if (tpr > 1024) tpr = 1024;
+    int rgroups = 1024 / tpr;
+    if (rgroups > interior / ctas + 2) rgroups = interior / ctas + 2;
+    if (rgroups < 1) rgroups = 1;
+    int dev_smem = 0, coop = 0, per_sm = 0;
+    CK(cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->p.device));
+    CK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, h->p.device));
+    size_t smem = 0;
+    for (;; G--) { // fewer updates per exchange if the ghost zones do not fit
+        smem = 2 * (size_t)(interior / ctas + 1 + 2 * G) * h->pitch * sizeof(float);
+        if (smem <= (size_t)dev_smem || G == 1) break;
+    }
+    if (!coop || smem > (size_t)dev_smem) return 1; // does not fit: not an error
+    CK(cudaFuncSetAttribute(heat_resident<ARITH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, heat_resident<ARITH>, tpr * rgroups, smem));
+    if (per_sm < 1) return 1;
+    CK(cudaMalloc((void**)&h->res_halo, (size_t)ctas * 4 * G * h->pitch * sizeof(float)));
+    CK(cudaMalloc((void**)&h->res_flags, (size_t)ctas * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(h->res_flags, 0, (size_t)ctas * sizeof(unsigned long long), h->stream));
+    h->res_ctas = ctas;
+    h->res_threads = tpr * rgroups;
+    h->res_tpr = tpr;
+    h->res_ghost = G;
+    h->res_smem = smem;
+    return HEAT_OK;
+}
+
+// > 0: cannot be used for this handle; 0: ready; < 0: error
+static int resident_prepare(heat_handle* h)
+{
+    if (h->res_ctas > 0) return HEAT_OK;
+    if (h->res_ctas < 0 || !h->use_resident || h->p.nranks != 1 || h->nloc < 3 || h->p.ny < 3) return 1;
+    int rc;
+    switch (h->p.arith) {
+    case HEAT_F32_FMA: rc = resident_prepare_t<HEAT_ARITH_F32_FMA>(h); break;
+    case HEAT_F32_NOFMA: rc = resident_prepare_t<HEAT_ARITH_F32_NOFMA>(h); break;
+    default: rc = resident_prepare_t<HEAT_ARITH_F64MIX>(h); break;
+    }
+    if (rc > 0) h->res_ctas = -1; // remember that it does not fit
+    return rc;
+}
+
+static int launch_resident(heat_handle* h, int updates)
+{
+    resident_args a;
+    const int new_cur = h->cur ^ (updates & 1);
+    a.in = h->buf[h->cur];
+    a.out_final = h->buf[new_cur];
+    a.out_prev = h->buf[1 - new_cur];
+    a.nrows = h->nloc;
+    a.ny = h->p.ny;
+    a.pitch = h->pitch;
+    a.steps = updates;
+    a.ghost = h->res_ghost;
+    a.threads_per_row = h->res_tpr;
+    a.cx = h->p.cx;
+    a.cy = h->p.cy;
+    a.halo = h->res_halo;
+    a.flags = h->res_flags;
+    a.epoch0 = h->res_epoch;
+    a.status = h->d_status;
+    a.timeout_ns = WAIT_TIMEOUT_NS;
+    void* kargs[] = {&a};
+    const void* fn = h->p.arith == HEAT_F32_FMA     ? (const void*)heat_resident<HEAT_ARITH_F32_FMA>
+                     : h->p.arith == HEAT_F32_NOFMA ? (const void*)heat_resident<HEAT_ARITH_F32_NOFMA>
+                                                    : (const void*)heat_resident<HEAT_ARITH_F64MIX>;
+    CK(cudaLaunchCooperativeKernel(fn, dim3(h->res_ctas), dim3(h->res_threads), kargs, h->res_smem, h->stream));
+    h->res_epoch += (unsigned long long)updates; // an upper bound of the exchanges made: flags stay monotonic
+    h->cur = new_cur;
+    h->it += updates;
+    h->sweeps += updates;
+    h->seq += (unsigned long long)updates;
+    h->launches++;
+    return HEAT_OK;
+}
+
 // GRAPH_PASSES consecutive passes as one CUDA graph (captured on a side stream, launched on the
 // handle's stream).  Replaces per-kernel launches where they dominate: the loop of C:204-211 costs
 // one launch per update, 2-4 us each in the reference's own Table 6.
@@ -594,6 +698,18 @@ extern "C" int heat_group_enqueue(heat_handle** hs, int n, int updates)
     const int T = hs[0]->p.temporal_block;
     for (int i = 0; i < updates;) {
         const int fused = (T > 1 && updates - i >= T) ? T : 1;
+        // small grids: the field stays in shared memory for all the remaining updates of this stretch
+        if (n == 1 && updates - i >= RESIDENT_MIN_UPDATES) {
+            CK(cudaSetDevice(hs[0]->p.device));
+            int rc = resident_prepare(hs[0]);
+            if (rc < 0) return rc;
+            if (rc == 0) {
+                if (launch_resident(hs[0], updates - i) == HEAT_OK) break;
+                // e.g. the GPU cannot co-schedule the CTAs right now: use ordinary passes from here on
+                cudaGetLastError();
+                hs[0]->res_ctas = -1;
+            }
+        }
         // a single strip replays a captured graph of GRAPH_PASSES passes while enough updates are left
         // (the launch-bound regime of small grids; state is unchanged after an even number of passes)
         if (n == 1 && hs[0]->p.nranks == 1 && hs[0]->use_graphs && updates - i >= GRAPH_PASSES * fused) {

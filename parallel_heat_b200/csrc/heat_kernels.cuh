@@ -569,6 +569,176 @@ heat_step_tb(const float* __restrict__ in, float* __restrict__ out, int nrows, i
     if (SYNC) strip_signal(sy, edge_n, edge_s);
 }
 
+// ------------------------------------------------------------------ K5 resident field (small grids)
+// For grids whose field fits in the shared memory of the whole chip (up to about 1700^2) a pass over
+// HBM per update is not the cost -- the launch is (C:204-211 pays one per update; the reference's own
+// Table 6 sits at 2-4 us per update).  One cooperative launch runs `steps` updates: CTA b (one per
+// SM) keeps its band of rows plus G ghost rows each side in shared memory, in two copies (old /
+// new).  It updates the band G times in a row -- the valid part of the ghost zone shrinks by one row
+// per update, exactly like the temporal blocking of K4 -- and only then exchanges rows with its two
+// neighbours: it publishes its first and last G owned rows in a small global scratch, raises its
+// flag (st.release.gpu), waits for the neighbours' flags and copies their rows into its ghost zones.
+// Only neighbours synchronise (about 3 us per exchange, hence G updates per exchange); the
+// cooperative launch guarantees that all CTAs are resident.  Rows are streamed like in K1 (float4
+// per lane, N/C/S in registers, E/W by shuffle), several row groups per CTA working in parallel.
+// At the end the last two states go back to the two global buffers.
+struct resident_args {
+    const float* in;    // newest field (global, pitch-strided)
+    float* out_final;   // receives the state after `steps` updates
+    float* out_prev;    // receives the state after steps-1 updates (keeps heat_residual meaningful)
+    int nrows, ny;
+    int64_t pitch;
+    int steps;
+    int ghost;          // G: updates per exchange = ghost rows per side (<= rows of the shortest band)
+    int threads_per_row; // threads that share one row (multiple of 32); blockDim.x / this = row groups
+    float cx, cy;
+    float* halo;                 // [P][2 sides][2 parities][G][pitch]
+    unsigned long long* flags;   // [P] exchanges completed by CTA b (monotonic over launches)
+    unsigned long long epoch0;
+    int* status;
+    unsigned long long timeout_ns;
+};
+
+__device__ __forceinline__ void spin_until_gpu(const unsigned long long* f, unsigned long long value,
+                                               unsigned long long timeout_ns, int* status)
+{
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    unsigned spins = 0;
+    for (;;) {
+        unsigned long long v;
+        asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+        if (v >= value) return;
+        if ((++spins & 1023u) == 0) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (t - t0 > timeout_ns) {
+                *status = 1;
+                __threadfence_system();
+                return;
+            }
+        }
+    }
+}
+
+template <int ARITH>
+__global__ void __launch_bounds__(1024, 1) heat_resident(resident_args a)
+{
+    extern __shared__ float4 resident_smem[];
+    float* sm = reinterpret_cast<float*>(resident_smem);
+    const unsigned FULL = 0xffffffffu;
+    const int P = gridDim.x, b = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
+    const int W = (int)a.pitch, G = a.ghost, ncg = W / 4;
+    // balanced split of the interior rows 1..nrows-2 over the P CTAs
+    const int interior = a.nrows - 2, base = interior / P, rem = interior % P;
+    const int r_lo = 1 + b * base + min(b, rem), rb = base + (b < rem ? 1 : 0);
+    // ghost zones: G rows towards a neighbouring CTA, the single (constant) ring row at the two ends
+    const bool top_fixed = (b == 0), bot_fixed = (b == P - 1);
+    const int gt = top_fixed ? 1 : G, gb = bot_fixed ? 1 : G;
+    const int R = rb + gt + gb;            // local rows; owned rows are gt .. gt+rb-1
+    const int copy = (base + 1 + 2 * G) * W; // floats per copy (tallest band); copy k starts at sm + k*copy
+
+    // both copies start as the field: ring columns and padding are then never written again
+    for (int k = tid; k < R * ncg; k += blockDim.x) {
+        const int lr = k / ncg, c4 = k - lr * ncg;
+        const float4 v = ld4(a.in + (int64_t)(r_lo - gt + lr) * a.pitch + c4 * 4);
+        st4(sm + lr * W + c4 * 4, v);
+        st4(sm + copy + lr * W + c4 * 4, v);
+    }
+    __syncthreads();
+
+    const int tpr = a.threads_per_row, rgroups = blockDim.x / tpr, rg = tid / tpr, ct = tid - rg * tpr;
+    float* const halo_mine = a.halo + (size_t)b * 4 * G * W;
+    unsigned long long exchanges = a.epoch0;
+    int s = 0;
+    while (s < a.steps) {
+        const int g = min(G, a.steps - s);
+        for (int k = 0; k < g; k++) {
+            const float* old = sm + ((s + k) & 1) * copy;
+            float* nw = sm + (((s + k) & 1) ^ 1) * copy;
+            // rows that can still be computed from valid neighbours: the zone shrinks towards the band
+            const int lo = top_fixed ? 1 : k + 1, hi = bot_fixed ? R - 2 : R - 2 - k;
+            const int chunk = (hi - lo + 1 + rgroups - 1) / rgroups;
+            const int my_lo = lo + rg * chunk, my_hi = min(my_lo + chunk - 1, hi);
+            if (my_lo <= my_hi) {
+                for (int cg0 = (ct & ~31); cg0 < ncg; cg0 += tpr) {
+                    int cg = cg0 + lane;
+                    const bool live = cg < ncg;
+                    if (!live) cg = ncg - 1;
+                    const int col = cg * 4;
+                    const bool kx = (col == 0) || (col >= a.ny - 1), ky = (col + 1 >= a.ny - 1), kz = (col + 2 >= a.ny - 1),
+                               kw = (col + 3 >= a.ny - 1);
+                    const bool e0 = lane == 0 && col > 0, e31 = lane == 31 && col + 4 < W;
+                    float4 n = ld4(old + (my_lo - 1) * W + col), c = ld4(old + my_lo * W + col);
+                    for (int i = my_lo; i <= my_hi; i++) {
+                        const float4 sd = ld4(old + (i + 1) * W + col);
+                        float wl = __shfl_up_sync(FULL, c.w, 1);
+                        float er = __shfl_down_sync(FULL, c.x, 1);
+                        if (e0) wl = old[i * W + col - 1];
+                        if (e31) er = old[i * W + col + 4];
+                        float4 o;
+                        o.x = upd<ARITH>(c.x, n.x, sd.x, c.y, wl, a.cx, a.cy);
+                        o.y = upd<ARITH>(c.y, n.y, sd.y, c.z, c.x, a.cx, a.cy);
+                        o.z = upd<ARITH>(c.z, n.z, sd.z, c.w, c.y, a.cx, a.cy);
+                        o.w = upd<ARITH>(c.w, n.w, sd.w, er, c.z, a.cx, a.cy);
+                        if (kx) o.x = c.x;
+                        if (ky) o.y = c.y;
+                        if (kz) o.z = c.z;
+                        if (kw) o.w = c.w;
+                        if (live) st4(nw + i * W + col, o);
+                        n = c;
+                        c = sd;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        s += g;
+        if (s == a.steps) break; // nothing left to exchange for
+        // ---- exchange: my first / last G owned rows of the current state go to the neighbours
+        float* cur = sm + (s & 1) * copy;
+        const int par = (int)(exchanges & 1);
+        for (int k = tid; k < G * ncg; k += blockDim.x) {
+            const int lr = k / ncg, c4 = k - lr * ncg;
+            if (!top_fixed)
+                __stcg(reinterpret_cast<float4*>(halo_mine + ((0 * 2 + par) * G + lr) * W) + c4,
+                       *reinterpret_cast<const float4*>(cur + (gt + lr) * W + c4 * 4));
+            if (!bot_fixed)
+                __stcg(reinterpret_cast<float4*>(halo_mine + ((1 * 2 + par) * G + lr) * W) + c4,
+                       *reinterpret_cast<const float4*>(cur + (gt + rb - G + lr) * W + c4 * 4));
+        }
+        __syncthreads();
+        exchanges++;
+        if (tid == 0) {
+            __threadfence();
+            asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(a.flags + b), "l"(exchanges) : "memory");
+            if (!top_fixed) spin_until_gpu(a.flags + b - 1, exchanges, a.timeout_ns, a.status);
+            if (!bot_fixed) spin_until_gpu(a.flags + b + 1, exchanges, a.timeout_ns, a.status);
+        }
+        __syncthreads();
+        // the north neighbour's last G rows are my top ghost zone, the south neighbour's first G rows my bottom one
+        for (int k = tid; k < G * ncg; k += blockDim.x) {
+            const int lr = k / ncg, c4 = k - lr * ncg;
+            if (!top_fixed)
+                st4(cur + lr * W + c4 * 4,
+                    __ldcg(reinterpret_cast<const float4*>(a.halo + (((size_t)(b - 1) * 4 + 1 * 2 + par) * G + lr) * W) + c4));
+            if (!bot_fixed)
+                st4(cur + (gt + rb + lr) * W + c4 * 4,
+                    __ldcg(reinterpret_cast<const float4*>(a.halo + (((size_t)(b + 1) * 4 + 0 * 2 + par) * G + lr) * W) + c4));
+        }
+        __syncthreads();
+    }
+    // ---- the last two states go back to HBM (owned rows only; ring rows never change)
+    const float* fin = sm + (a.steps & 1) * copy;
+    const float* prev = sm + ((a.steps & 1) ^ 1) * copy;
+    for (int k = tid; k < rb * ncg; k += blockDim.x) {
+        const int lr = gt + k / ncg, c4 = k - (lr - gt) * ncg;
+        const int64_t g = (int64_t)(r_lo - gt + lr) * a.pitch + c4 * 4;
+        st4(a.out_final + g, ld4(fin + lr * W + c4 * 4));
+        if (a.out_prev) st4(a.out_prev + g, ld4(prev + lr * W + c4 * 4));
+    }
+}
+
 // ------------------------------------------------------------------ residual of two buffers
 // max |a-b| over the interior of a strip (heat_residual(): a separate pass, not on the hot path)
 __global__ void __launch_bounds__(256)
