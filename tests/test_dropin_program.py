@@ -66,3 +66,14 @@ def test_cuda_style_file_name_and_strips(programs, oracle, tmp_path):
     assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
     # several strips on one GPU through the same program would need several devices; the group API
     # itself is covered by test_gpu_parity.py::test_strip_decomposition_is_bit_identical
+
+
+def test_sized_binaries_like_the_reference_makefile(ph, tmp_path):
+    # mpi/Makefile:6-22 builds heat_<SIZE> and heat_con_<SIZE> with the sizes baked in; so does src/Makefile
+    subprocess.run(["make", "-s", "-C", str(SRC), "sized", "SIZE=64", "STEPS=300", "STEP=20"], check=True)
+    out, _ = run(SRC / "heat_64", tmp_path, "--no-dump")
+    assert "Grid size: X= 64  Y= 64  Time steps= 300" in out
+    out, _ = run(SRC / "heat_con_64", tmp_path, "--no-dump")
+    assert "Grid size: X= 64  Y= 64  Time steps= - " in out and ("Converged after" in out or "Didn't converged" in out)
+    for f in ("heat_64", "heat_con_64"):
+        (SRC / f).unlink()

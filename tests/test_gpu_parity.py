@@ -520,3 +520,27 @@ def test_resident_kernel_keeps_the_handle_consistent(ph, oracle):
     b, _, _ = oracle.solve(u, 61, arith=2)
     assert_same_bits(got, b)
     assert r == oracle.max_abs_diff(a, b)
+
+
+# ---------------------------------------------------------------- randomized differential test
+def test_random_configurations_match_the_oracle(ph, oracle):
+    # 160 random (shape, steps, arithmetic, coefficients, fused updates, strips, convergence) cases, fixed seed
+    rng = np.random.default_rng(20261106)
+    for case in range(160):
+        nx, ny = int(rng.integers(3, 180)), int(rng.integers(3, 700))
+        arith = int(rng.integers(0, 3))
+        T = int(rng.integers(1, 5))
+        steps = int(rng.integers(0, 14))
+        cx, cy = (float(np.float32(v)) for v in rng.uniform(0.0, 0.24, 2))
+        K = int(rng.choice([0, 0, 3, 5]))
+        phase, conv_steps = int(rng.integers(0, 2)), int(rng.integers(0, 2))
+        u = (rng.standard_normal((nx, ny)) * float(rng.choice([1e-3, 1.0, 1e4]))).astype(np.float32)
+        kw = dict(arith=arith, cx=cx, cy=cy, conv_every=K, conv_phase=phase, step_convention=conv_steps)
+        want, wdone, wconv = oracle.solve(u, steps, **kw)
+        g = int(rng.integers(1, 4))
+        if g > 1 and nx // g >= max(2, T) and K == 0:
+            got, done, conv = run_strips(ph, u, g, steps, temporal_block=T, **kw)
+        else:
+            got, done, conv = ph.solve(u, steps, temporal_block=T, **kw)
+        assert (done, conv) == (wdone, wconv), (case, nx, ny, kw, T, g)
+        assert_same_bits(got, want, f"case {case}: {nx}x{ny} steps={steps} T={T} strips={g} {kw}")
