@@ -70,6 +70,12 @@ const char *heat_last_error(void);
 /* 1 if a CUDA device is usable by this process, else 0 (never fails). */
 int heat_device_count(void);
 
+/* Environment variables read when a handle is created (tuning and debugging; defaults are the measured
+ * best): HEAT_ROWS_PER_TILE (K1/K2 tile height, 8), HEAT_ROWS_PER_TILE_TB (K4 tile height, by row length),
+ * HEAT_SERPENTINE (alternate sweep direction, 1), HEAT_GRAPHS (CUDA graphs of 16 passes, 1),
+ * HEAT_RESIDENT (field resident in shared memory for grids that fit, 1), HEAT_RESIDENT_G (updates per
+ * neighbour exchange of that kernel, 6), HEAT_TIMING (heat_solve prints its phases to stderr, 0). */
+
 /* ---- the reference's helpers, same arguments (M:315-341, C:274-300) ------------------ */
 /* inidat: u[ix*ny+iy] = (float)(ix*(nx-ix-1)*iy*(ny-iy-1)) in wrapping int32 (M:320). */
 int heat_inidat(int nx, int ny, float *u);

@@ -378,13 +378,12 @@ static int pick_rows_per_tile(const heat_handle* h, int threads)
 // how many CTAs touch the north / south neighbour (same predicate as edge_n / edge_s in the kernels)
 static void count_edge_ctas(heat_handle* h, int rows, int rpt, unsigned grid_x, unsigned tiles)
 {
-    unsigned tn = 0, ts = 0;
-    for (unsigned t = 0; t < tiles; t++) {
-        const int r0 = (int)t * rpt, r1 = (r0 + rpt < rows) ? r0 + rpt : rows; // relative to upd_lo
-        if (r0 < h->ghost) tn++;
-        if (r1 > rows - h->ghost) ts++;
-        if (r0 >= h->ghost && t + 8 < tiles) t = tiles - 9; // only the ends can qualify: skip the middle
-    }
+    // tile t covers rows [t*rpt, min((t+1)*rpt, rows)) relative to upd_lo
+    const unsigned g = (unsigned)h->ghost;
+    unsigned tn = (g + rpt - 1) / rpt;                               // tiles with r0 < ghost
+    const unsigned first_s = rows > (int)g ? (unsigned)(rows - g) / rpt : 0; // first tile with r1 > rows - ghost
+    if (tn > tiles) tn = tiles;
+    const unsigned ts = tiles - (first_s < tiles ? first_s : tiles);
     h->sync_args.count_n = tn * grid_x;
     h->sync_args.count_s = ts * grid_x;
 }
@@ -662,6 +661,7 @@ static int launch_pass_graph(heat_handle* h, int fused)
         if (!h->capture_stream) CK(cudaStreamCreateWithFlags(&h->capture_stream, cudaStreamNonBlocking));
         const cudaStream_t user = h->stream;
         const long long it0 = h->it, sweeps0 = h->sweeps;
+        const int cur0 = h->cur;
         const unsigned long long seq0 = h->seq;
         const int64_t launches0 = h->launches;
         cudaGraph_t graph = nullptr;
@@ -673,7 +673,7 @@ static int launch_pass_graph(heat_handle* h, int fused)
             e = cudaStreamEndCapture(h->capture_stream, &graph);
         }
         h->stream = user;
-        h->it = it0, h->sweeps = sweeps0, h->seq = seq0, h->launches = launches0; // nothing ran yet
+        h->it = it0, h->sweeps = sweeps0, h->seq = seq0, h->launches = launches0, h->cur = cur0; // nothing ran yet
         if (rc) {
             if (graph) cudaGraphDestroy(graph);
             return rc;
