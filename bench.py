@@ -221,19 +221,21 @@ def run_ours(args, wl, rank, world, local_rank):
 
     if world > 1:
         from parallel_heat_b200.strips import StripSolver
-        s = StripSolver(nx, ny, device=local_rank, halo=args.halo, **params)
+        s = StripSolver(nx, ny, device=local_rank, halo=args.halo, cols=args.cols, **params)
         solver = s.solver
         if args.halo == "p2p":
             solver.set_stream(stream.cuda_stream)
         s.init_inidat()
         enqueue, sync = s.enqueue, s.sync
         rows_own = s.rows
+        cols_own = s.ncols
     else:
         solver = api.HeatSolver(nx, ny, device=local_rank, **params)
         solver.set_stream(stream.cuda_stream)
         solver.init_inidat()
         enqueue, sync = solver.enqueue, solver.sync
         rows_own = nx
+        cols_own = ny
 
     def barrier():
         torch.cuda.synchronize()
@@ -271,7 +273,7 @@ def run_ours(args, wl, rank, world, local_rank):
     # roofline of the dominant kernel (the update kernel): this rank's algorithmic bytes per launch
     peak, peak_src = measured_peak()
     step_launches = K // wl["temporal_block"] if wl["temporal_block"] > 1 else K
-    own_lups = (min(rows_own, nx - 2) if world > 1 else nx - 2) * (ny - 2) * wl["temporal_block"]
+    own_lups = (min(rows_own, nx - 2) if world > 1 else nx - 2) * min(cols_own, ny - 2) * wl["temporal_block"]
     kernel_ms = ms / max(step_launches, 1)
     achieved = BYTES_PER_LUP * own_lups / (kernel_ms * 1e-3) / 1e9
     kname = "heat_step_tb" if wl["temporal_block"] > 1 else "heat_step_vec"
@@ -301,7 +303,7 @@ def run_ours(args, wl, rank, world, local_rank):
                "call": f"heat_solve(steps={K}) on pinned host memory: cudaMalloc + H2D of the {nx * ny * 4 >> 20} MiB field "
                        f"+ {done.value} updates + D2H, wall clock", "seconds": dt}
         launches_e2e = done.value
-    elif world > 1 and not args.no_e2e:
+    elif world > 1 and not args.no_e2e and args.cols == 1:
         # strips: every rank brings its own window of the field in pinned host memory, uploads it,
         # runs K updates and reads its rows back; wall clock between barriers (max over ranks)
         _, _, nloc, lo = solver.device_view(0)
@@ -386,6 +388,7 @@ def run_ours(args, wl, rank, world, local_rank):
                                         "computes in MPI_F64MIX (see also.mpi_f64mix); the two differ by < 1e-5 relative",
                           "conv_every": wl["conv_every"], "temporal_block": wl["temporal_block"],
                           "halo": (args.halo if world > 1 else "none"),
+                          "decomposition": (f"{world // args.cols}x{args.cols} blocks" if world > 1 else "single"),
                           "l2": f"working set {2 * nx * ny * 4 >> 20} MiB vs 126 MB L2: inputs larger than L2, no flush "
                                 "(consecutive updates ARE the workload)"},
                "roofline": roofline, "cpu_baseline": base, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
@@ -406,6 +409,7 @@ def main():
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--arith", choices=["fma", "nofma", "f64mix"], default="fma")
     ap.add_argument("--halo", choices=["p2p", "sendrecv"], default="p2p")
+    ap.add_argument("--cols", type=int, default=1, help="N>1: 2-D blocks with this many column blocks (default: row strips)")
     ap.add_argument("--temporal-block", type=int, default=0, help="override the workload's updates per HBM pass (1, 2, 4)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")

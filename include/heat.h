@@ -58,6 +58,7 @@ typedef struct heat_params {
     int   temporal_block;  /* updates fused per pass over HBM: 1 to 4                  */
     int   device;          /* CUDA device ordinal of this strip                        */
     int   rank, nranks;    /* row-strip decomposition: this handle owns strip `rank`   */
+    int   rank_y, nranks_y;/* column blocks on top of that (2-D blocks, M:51-75); 0, 1 = row strips only */
 } heat_params;
 
 typedef struct heat_handle heat_handle; /* opaque: owns device buffers, stream, graphs */
@@ -184,6 +185,14 @@ int heat_ipc_connect(heat_handle *h, const void *north_blob, const void *south_b
  * update by update, through heat_group_run / heat_group_enqueue; upload every strip first. */
 int heat_connect_local(heat_handle *h, heat_handle *north, heat_handle *south);
 int heat_group_run(heat_handle **strips, int n, int steps, int *updates_done, int *converged);
+/* 2-D blocks -- the reference's own cartesian topology (MPI_Cart_create, M:51-69; col_type halos,
+ * M:82-84,139-155): block (rank, rank_y) of nranks x nranks_y also has a west and an east neighbour and
+ * keeps one ghost column towards each; its first/last owned column is stored into the neighbour's ghost
+ * column by the update kernel (one float per row).  temporal_block must be 1.  Inside one NVSwitch box row
+ * strips are the better choice (contiguous halos); blocks are for what comes after it. */
+int heat_connect_local2d(heat_handle *h, heat_handle *north, heat_handle *south, heat_handle *west, heat_handle *east);
+int heat_ipc_connect2d(heat_handle *h, const void *north_blob, const void *south_blob, const void *west_blob,
+                       const void *east_blob);
 int heat_group_enqueue(heat_handle **strips, int n, int updates);
 /* Convergence across strips in OTHER processes: every conv_every updates heat_run hands the
  * local max|old-new| to this callback, which must return the maximum over all strips in

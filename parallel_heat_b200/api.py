@@ -39,7 +39,7 @@ class HeatParams(C.Structure):
     _fields_ = [("nx", C.c_int), ("ny", C.c_int), ("steps", C.c_int), ("cx", C.c_float), ("cy", C.c_float),
                 ("conv_every", C.c_int), ("conv_eps", C.c_float), ("conv_phase", C.c_int),
                 ("step_convention", C.c_int), ("arith", C.c_int), ("temporal_block", C.c_int),
-                ("device", C.c_int), ("rank", C.c_int), ("nranks", C.c_int)]
+                ("device", C.c_int), ("rank", C.c_int), ("nranks", C.c_int), ("rank_y", C.c_int), ("nranks_y", C.c_int)]
 
 
 ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.POINTER(C.c_float), C.c_void_p)
@@ -85,6 +85,8 @@ SIGNATURES = {
     "heat_ipc_export": (C.c_int, [_H, C.c_void_p, C.c_size_t]),
     "heat_ipc_connect": (C.c_int, [_H, C.c_void_p, C.c_void_p]),
     "heat_connect_local": (C.c_int, [_H, _H, _H]),
+    "heat_connect_local2d": (C.c_int, [_H, _H, _H, _H, _H]),
+    "heat_ipc_connect2d": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "heat_group_run": (C.c_int, [C.POINTER(_H), C.c_int, C.c_int, _ip, _ip]),
     "heat_group_enqueue": (C.c_int, [C.POINTER(_H), C.c_int, C.c_int]),
     "heat_set_allreduce_max": (C.c_int, [_H, ALLREDUCE_FN, C.c_void_p]),
@@ -284,13 +286,13 @@ class HeatSolver:
         _check(load().heat_ipc_export(self._h, blob, IPC_BLOB_BYTES))
         return blob.raw
 
-    def ipc_connect(self, north_blob, south_blob):
-        self._blobs = (C.create_string_buffer(north_blob, IPC_BLOB_BYTES) if north_blob else None,
-                       C.create_string_buffer(south_blob, IPC_BLOB_BYTES) if south_blob else None)
-        _check(load().heat_ipc_connect(self._h, self._blobs[0], self._blobs[1]))
+    def ipc_connect(self, north_blob, south_blob, west_blob=None, east_blob=None):
+        self._blobs = tuple(C.create_string_buffer(b, IPC_BLOB_BYTES) if b else None
+                            for b in (north_blob, south_blob, west_blob, east_blob))
+        _check(load().heat_ipc_connect2d(self._h, *self._blobs))
 
-    def connect_local(self, north, south):
-        _check(load().heat_connect_local(self._h, north._h if north else None, south._h if south else None))
+    def connect_local(self, north, south, west=None, east=None):
+        _check(load().heat_connect_local2d(self._h, *[o._h if o else None for o in (north, south, west, east)]))
 
     def set_allreduce_max(self, fn):
         """fn(value: float) -> float, the maximum over every strip's value."""

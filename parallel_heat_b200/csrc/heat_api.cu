@@ -62,6 +62,8 @@ extern "C" int heat_params_default(heat_params* p)
     p->device = 0;
     p->rank = 0;
     p->nranks = 1;
+    p->rank_y = 0;
+    p->nranks_y = 1;
     return HEAT_OK;
 }
 
@@ -154,7 +156,8 @@ extern "C" int heat_strip_rows(int nx, int nranks, int rank, int* row0, int* row
 struct peer_side {
     float* buf[2] = {nullptr, nullptr};   // neighbour's two buffers (peer-mapped)
     unsigned long long* flag = nullptr;   // neighbour's flag slot that this strip writes
-    int nloc = 0;
+    int nloc = 0, nyloc = 0;
+    int64_t pitch = 0;
     void* ipc_base[3] = {nullptr, nullptr, nullptr}; // bases opened with cudaIpcOpenMemHandle
 };
 
@@ -164,6 +167,8 @@ struct heat_handle {
     int lo = 0, nloc = 0;       // local array = global rows [lo, lo+nloc)
     int ghost = 1;              // ghost rows kept towards each neighbour (= temporal_block)
     int upd_lo = 1, upd_hi = 0; // local rows [upd_lo, upd_hi) are the ones this strip updates
+    int col0 = 0, cols_own = 0; // owned global columns [col0, col0+cols_own) (2-D blocks; else all)
+    int lo_c = 0, nyloc = 0;    // local array = global columns [lo_c, lo_c+nyloc): + one ghost column per neighbour
     int64_t pitch = 0;          // floats
     float* buf[2] = {nullptr, nullptr};
     int cur = 0;                // index of the newest buffer
@@ -185,11 +190,12 @@ struct heat_handle {
     // neighbours: side 0 = north (lower rows), 1 = south
     unsigned* d_edge_count = nullptr;    // [2] edge-CTA arrival counters of the fused strip ordering
     strip_sync sync_args = {};           // filled per pass for flag-ordered strips, else all null
-    unsigned long long* flags = nullptr; // [0] written by north neighbour, [1] by south
-    peer_side peer[2];
+    col_peers col_args = {};             // 2-D blocks: where my first / last owned column goes
+    unsigned long long* flags = nullptr; // [0] written by the north neighbour, [1] south, [2] west, [3] east
+    peer_side peer[4];
     bool connected = false;
     // neighbours in this process are ordered with events instead of flags (no spinning kernels)
-    heat_handle* local_nb[2] = {nullptr, nullptr};
+    heat_handle* local_nb[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev_done[2] = {nullptr, nullptr}; // recorded after epoch e in ev_done[e & 1]
     bool serpentine = true;
     // CUDA graphs of GRAPH_PASSES consecutive passes, one per (newest buffer, sweep direction, fused?)
@@ -212,7 +218,7 @@ struct ipc_blob {
     char magic[8];
     cudaIpcMemHandle_t mem[3]; // buf0, buf1, flags
     int64_t offset[3];         // of the pointer inside the exported allocation
-    int32_t nloc, rank, nranks, pad;
+    int32_t nloc, rank, nranks, nyloc, rank_y, nranks_y;
     int64_t pitch;
 };
 static_assert(sizeof(ipc_blob) <= HEAT_IPC_BLOB_BYTES, "ipc blob too large");
@@ -237,6 +243,10 @@ static int validate(const heat_params* p)
     if (p->nranks > 1 && p->nx / p->nranks < (p->temporal_block > 2 ? p->temporal_block : 2))
         return fail(HEAT_E_INVALID, "params: %d rows cannot be cut into %d strips of >= %d rows", p->nx, p->nranks,
                     p->temporal_block > 2 ? p->temporal_block : 2);
+    if (p->nranks_y < 1 || p->rank_y < 0 || p->rank_y >= p->nranks_y)
+        return fail(HEAT_E_INVALID, "params: rank_y=%d nranks_y=%d", p->rank_y, p->nranks_y);
+    if (p->nranks_y > 1 && (p->ny / p->nranks_y < 2 || p->temporal_block != 1))
+        return fail(HEAT_E_INVALID, "params: column blocks need >= 2 columns each and temporal_block 1");
     if (p->conv_phase != HEAT_PHASE_MPI && p->conv_phase != HEAT_PHASE_CUDA)
         return fail(HEAT_E_INVALID, "params: conv_phase=%d", p->conv_phase);
     if (p->step_convention != HEAT_STEPS_CUDA && p->step_convention != HEAT_STEPS_MPI)
@@ -249,7 +259,7 @@ extern "C" int heat_destroy(heat_handle* h)
     if (!h) return HEAT_OK;
     cudaSetDevice(h->p.device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    for (int s = 0; s < 2; s++)
+    for (int s = 0; s < 4; s++)
         for (int k = 0; k < 3; k++)
             if (h->peer[s].ipc_base[k]) cudaIpcCloseMemHandle(h->peer[s].ipc_base[k]);
     if (h->buf[0]) cudaFree(h->buf[0]);
@@ -300,8 +310,14 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     h->nloc = hi - h->lo;
     h->upd_lo = (p->rank > 0) ? h->ghost : 1;
     h->upd_hi = (p->rank < p->nranks - 1) ? h->nloc - h->ghost : h->nloc - 1;
+    // 2-D blocks (the reference's topology, M:51-75): the same split along the columns, one ghost column
+    // per neighbour; a single column block keeps all columns and the ring columns are its own
+    heat_strip_rows(p->ny, p->nranks_y, p->rank_y, &h->col0, &h->cols_own);
+    h->lo_c = (p->rank_y > 0) ? h->col0 - 1 : 0;
+    const int hi_c = (p->rank_y < p->nranks_y - 1) ? h->col0 + h->cols_own + 1 : p->ny;
+    h->nyloc = hi_c - h->lo_c;
     // rows padded to 128 bytes so that every row starts on a float4 (and a cache line)
-    h->pitch = ((int64_t)p->ny + 31) / 32 * 32;
+    h->pitch = ((int64_t)h->nyloc + 31) / 32 * 32;
 
     const size_t bytes = (size_t)h->nloc * h->pitch * sizeof(float);
 #define CKH(call)                                                                                      \
@@ -316,9 +332,9 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     } while (0)
     CKH(cudaMalloc((void**)&h->buf[0], bytes));
     CKH(cudaMalloc((void**)&h->buf[1], bytes));
-    CKH(cudaMalloc((void**)&h->flags, 2 * sizeof(unsigned long long)));
+    CKH(cudaMalloc((void**)&h->flags, 4 * sizeof(unsigned long long)));
     CKH(cudaMalloc((void**)&h->d_resid, sizeof(unsigned)));
-    CKH(cudaMalloc((void**)&h->d_edge_count, 2 * sizeof(unsigned)));
+    CKH(cudaMalloc((void**)&h->d_edge_count, 4 * sizeof(unsigned)));
     CKH(cudaHostAlloc((void**)&h->h_resid, sizeof(unsigned), cudaHostAllocDefault));
     CKH(cudaHostAlloc((void**)&h->h_status, sizeof(int), cudaHostAllocMapped));
     *h->h_status = 0;
@@ -327,9 +343,9 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     h->own_stream = true;
     CKH(cudaMemsetAsync(h->buf[0], 0, bytes, h->stream));
     CKH(cudaMemsetAsync(h->buf[1], 0, bytes, h->stream));
-    CKH(cudaMemsetAsync(h->flags, 0, 2 * sizeof(unsigned long long), h->stream));
+    CKH(cudaMemsetAsync(h->flags, 0, 4 * sizeof(unsigned long long), h->stream));
     CKH(cudaMemsetAsync(h->d_resid, 0, sizeof(unsigned), h->stream));
-    CKH(cudaMemsetAsync(h->d_edge_count, 0, 2 * sizeof(unsigned), h->stream));
+    CKH(cudaMemsetAsync(h->d_edge_count, 0, 4 * sizeof(unsigned), h->stream));
     CKH(cudaEventCreate(&h->ev0));
     CKH(cudaEventCreate(&h->ev1));
     CKH(cudaEventCreateWithFlags(&h->ev_resid, cudaEventDisableTiming));
@@ -384,14 +400,15 @@ static void count_edge_ctas(heat_handle* h, int rows, int rpt, unsigned grid_x, 
     const unsigned first_s = rows > (int)g ? (unsigned)(rows - g) / rpt : 0; // first tile with r1 > rows - ghost
     if (tn > tiles) tn = tiles;
     const unsigned ts = tiles - (first_s < tiles ? first_s : tiles);
-    h->sync_args.count_n = tn * grid_x;
-    h->sync_args.count_s = ts * grid_x;
+    h->sync_args.count[0] = tn * grid_x;
+    h->sync_args.count[1] = ts * grid_x;
+    h->sync_args.count[2] = h->sync_args.count[3] = tiles; // one west-edge and one east-edge CTA per tile row
 }
 
 template <int ARITH, bool RESID>
 static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, float* peer_n, float* peer_s, int reverse)
 {
-    const int rows = h->upd_hi - h->upd_lo, ny = h->p.ny;
+    const int rows = h->upd_hi - h->upd_lo, ny = h->nyloc;
     if (rows < 1 || ny < 3) return cudaSuccess; // no interior: nothing to update (ring only)
 #ifndef HEAT_K1_THREADS
 #define HEAT_K1_THREADS 128
@@ -402,7 +419,16 @@ static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, fl
     if ((rows + rpt - 1) / rpt > 65535) rpt = (rows + 65534) / 65535; // grid.y limit: taller tiles
     dim3 grid((unsigned)((h->pitch / 4 + THREADS - 1) / THREADS), (unsigned)((rows + rpt - 1) / rpt));
     count_edge_ctas(h, rows, rpt, grid.x, grid.y);
-    if (h->sync_args.counters)
+    if (h->p.nranks_y > 1) { // 2-D blocks: column neighbours too
+        if (h->sync_args.counters)
+            heat_step_vec<ARITH, RESID, THREADS, UNROLL, true, true><<<grid, THREADS, 0, h->stream>>>(
+                in, out, h->upd_lo, h->upd_hi, ny, h->pitch, rpt, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse,
+                h->sync_args, h->col_args);
+        else
+            heat_step_vec<ARITH, RESID, THREADS, UNROLL, false, true><<<grid, THREADS, 0, h->stream>>>(
+                in, out, h->upd_lo, h->upd_hi, ny, h->pitch, rpt, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse,
+                h->sync_args, h->col_args);
+    } else if (h->sync_args.counters)
         heat_step_vec<ARITH, RESID, THREADS, UNROLL, true><<<grid, THREADS, 0, h->stream>>>(
             in, out, h->upd_lo, h->upd_hi, ny, h->pitch, rpt, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse,
             h->sync_args);
@@ -418,7 +444,7 @@ static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, fl
 template <int ARITH, int T>
 static cudaError_t launch_tb_t(heat_handle* h, const float* in, float* out, float* peer_n, float* peer_s, int reverse)
 {
-    const int rows = h->upd_hi - h->upd_lo, ny = h->p.ny;
+    const int rows = h->upd_hi - h->upd_lo, ny = h->nyloc;
     if (rows < 1 || ny < 3) return cudaSuccess;
 #ifndef HEAT_TB_WARPS
 #define HEAT_TB_WARPS 1 // warps per CTA of the temporal-blocking kernel: 1 beat 2 and 4 by 3-5 % (finer balance)
@@ -496,34 +522,47 @@ static const unsigned long long WAIT_TIMEOUT_NS = 20ull * 1000000000ull;
 // neighbours) -> [signal neighbours] -> swap
 static int enqueue_update(heat_handle* h, bool resid, int fused = 1)
 {
-    const bool has_n = !h->external_halo && h->p.rank > 0, has_s = !h->external_halo && h->p.rank < h->p.nranks - 1;
-    const bool strips = has_n || has_s;
+    // which neighbours exist: 0 north, 1 south (row blocks), 2 west, 3 east (column blocks)
+    const bool has[4] = {!h->external_halo && h->p.rank > 0, !h->external_halo && h->p.rank < h->p.nranks - 1,
+                         h->p.rank_y > 0, h->p.rank_y < h->p.nranks_y - 1};
+    const bool strips = has[0] || has[1] || has[2] || has[3];
     if (strips && !h->connected)
-        return fail(HEAT_E_PEER, "strip %d of %d is not connected to its neighbours", h->p.rank, h->p.nranks);
-    const bool local = h->local_nb[0] || h->local_nb[1];
+        return fail(HEAT_E_PEER, "block (%d,%d) of %dx%d is not connected to its neighbours", h->p.rank, h->p.rank_y, h->p.nranks,
+                    h->p.nranks_y);
+    const bool local = h->local_nb[0] || h->local_nb[1] || h->local_nb[2] || h->local_nb[3];
     const float* in = h->buf[h->cur];
     float* out = h->buf[1 - h->cur];
     float *pn = nullptr, *ps = nullptr;
+    h->col_args = col_peers{};
     if (strips) {
         if (local) {
             // neighbour's epoch `seq` (its previous update, or its upload) must be complete
-            for (int side = 0; side < 2; side++)
+            for (int side = 0; side < 4; side++)
                 if (h->local_nb[side]) CK(cudaStreamWaitEvent(h->stream, h->local_nb[side]->ev_done[h->seq & 1], 0));
         }
         // my first owned row (local row 1) is the north neighbour's bottom ghost row, and vice versa
-        if (has_n) pn = h->peer[0].buf[1 - h->cur] + (int64_t)(h->peer[0].nloc - h->ghost) * h->pitch;
-        if (has_s) ps = h->peer[1].buf[1 - h->cur];
+        if (has[0]) pn = h->peer[0].buf[1 - h->cur] + (int64_t)(h->peer[0].nloc - h->ghost) * h->pitch;
+        if (has[1]) ps = h->peer[1].buf[1 - h->cur];
+        // my first owned column is the west neighbour's last (ghost) column, my last its first
+        if (has[2]) {
+            h->col_args.w = h->peer[2].buf[1 - h->cur] + (h->peer[2].nyloc - 1);
+            h->col_args.pitch_w = h->peer[2].pitch;
+        }
+        if (has[3]) {
+            h->col_args.e = h->peer[3].buf[1 - h->cur];
+            h->col_args.pitch_e = h->peer[3].pitch;
+        }
     }
     if (resid) CK(cudaMemsetAsync(h->d_resid, 0, sizeof(unsigned), h->stream));
     // flag-ordered strips (one process per GPU): the wait and the signal are fused into the pass
     h->sync_args = strip_sync{};
     if (strips && !local) {
         strip_sync& sy = h->sync_args;
-        sy.wait_n = has_n ? &h->flags[0] : nullptr;
-        sy.wait_s = has_s ? &h->flags[1] : nullptr;
+        for (int side = 0; side < 4; side++) {
+            sy.wait[side] = has[side] ? &h->flags[side] : nullptr;
+            sy.sig[side] = has[side] ? h->peer[side].flag : nullptr;
+        }
         sy.wait_value = h->seq;
-        sy.sig_n = has_n ? h->peer[0].flag : nullptr;
-        sy.sig_s = has_s ? h->peer[1].flag : nullptr;
         sy.sig_value = h->seq + 1;
         sy.counters = h->d_edge_count;
         sy.status = h->d_status;
@@ -604,7 +643,7 @@ static int resident_prepare_t(heat_handle* h)
 static int resident_prepare(heat_handle* h)
 {
     if (h->res_ctas > 0) return HEAT_OK;
-    if (h->res_ctas < 0 || !h->use_resident || h->p.nranks != 1 || h->nloc < 3 || h->p.ny < 3) return 1;
+    if (h->res_ctas < 0 || !h->use_resident || h->p.nranks != 1 || h->p.nranks_y != 1 || h->nloc < 3 || h->p.ny < 3) return 1;
     int rc;
     switch (h->p.arith) {
     case HEAT_F32_FMA: rc = resident_prepare_t<HEAT_ARITH_F32_FMA>(h); break;
@@ -712,7 +751,7 @@ extern "C" int heat_group_enqueue(heat_handle** hs, int n, int updates)
         }
         // a single strip replays a captured graph of GRAPH_PASSES passes while enough updates are left
         // (the launch-bound regime of small grids; state is unchanged after an even number of passes)
-        if (n == 1 && hs[0]->p.nranks == 1 && hs[0]->use_graphs && updates - i >= GRAPH_PASSES * fused) {
+        if (n == 1 && hs[0]->p.nranks == 1 && hs[0]->p.nranks_y == 1 && hs[0]->use_graphs && updates - i >= GRAPH_PASSES * fused) {
             CK(cudaSetDevice(hs[0]->p.device));
             int rc = launch_pass_graph(hs[0], fused);
             if (rc) return rc;
@@ -732,7 +771,8 @@ extern "C" int heat_group_enqueue(heat_handle** hs, int n, int updates)
 extern "C" int heat_enqueue(heat_handle* h, int updates)
 {
     if (!h) return fail(HEAT_E_INVALID, "heat_enqueue: null handle");
-    if (h->local_nb[0] || h->local_nb[1]) return fail(HEAT_E_STATE, "heat_enqueue: locally connected strips run through heat_group_*");
+    if (h->local_nb[0] || h->local_nb[1] || h->local_nb[2] || h->local_nb[3])
+        return fail(HEAT_E_STATE, "heat_enqueue: locally connected strips run through heat_group_*");
     return heat_group_enqueue(&h, 1, updates);
 }
 
@@ -829,8 +869,9 @@ extern "C" int heat_group_run(heat_handle** hs, int n, int steps, int* updates_d
 extern "C" int heat_run(heat_handle* h, int steps, int* updates_done, int* converged)
 {
     if (!h) return fail(HEAT_E_INVALID, "heat_run: null handle");
-    if (h->local_nb[0] || h->local_nb[1]) return fail(HEAT_E_STATE, "heat_run: locally connected strips run through heat_group_run");
-    if (h->p.nranks > 1 && h->p.conv_every > 0 && !h->allreduce)
+    if (h->local_nb[0] || h->local_nb[1] || h->local_nb[2] || h->local_nb[3])
+        return fail(HEAT_E_STATE, "heat_run: locally connected strips run through heat_group_run");
+    if ((h->p.nranks > 1 || h->p.nranks_y > 1) && h->p.conv_every > 0 && !h->allreduce)
         return fail(HEAT_E_STATE, "heat_run: strips in several processes need heat_set_allreduce_max for the convergence check");
     return heat_group_run(&h, 1, steps, updates_done, converged);
 }
@@ -854,8 +895,8 @@ extern "C" int heat_residual(heat_handle* h, float* residual)
     if (!h || !residual) return fail(HEAT_E_INVALID, "heat_residual: bad arguments");
     CK(cudaSetDevice(h->p.device));
     CK(cudaMemsetAsync(h->d_resid, 0, sizeof(unsigned), h->stream));
-    if (h->upd_hi > h->upd_lo && h->p.ny >= 3) {
-        heat_absdiff_max<<<h->sm_count * 8, 256, 0, h->stream>>>(h->buf[0], h->buf[1], h->upd_lo, h->upd_hi, h->p.ny, h->pitch, h->d_resid);
+    if (h->upd_hi > h->upd_lo && h->nyloc >= 3) {
+        heat_absdiff_max<<<h->sm_count * 8, 256, 0, h->stream>>>(h->buf[0], h->buf[1], h->upd_lo, h->upd_hi, h->nyloc, h->pitch, h->d_resid);
         h->launches++;
         CK(cudaGetLastError());
     }
@@ -880,12 +921,13 @@ static int after_upload(heat_handle* h)
     // an upload counts as one epoch of the strip flags: neighbours may not store into this
     // strip's ghost rows before the upload has landed
     h->seq++;
-    const bool has_n = h->p.rank > 0, has_s = h->p.rank < h->p.nranks - 1;
-    if ((has_n || has_s) && h->connected && !h->external_halo) {
-        if (h->local_nb[0] || h->local_nb[1]) {
+    const bool has[4] = {h->p.rank > 0, h->p.rank < h->p.nranks - 1, h->p.rank_y > 0, h->p.rank_y < h->p.nranks_y - 1};
+    if ((has[0] || has[1] || has[2] || has[3]) && h->connected && !h->external_halo) {
+        if (h->local_nb[0] || h->local_nb[1] || h->local_nb[2] || h->local_nb[3]) {
             CK(cudaEventRecord(h->ev_done[h->seq & 1], h->stream));
         } else {
-            heat_signal<<<1, 32, 0, h->stream>>>(has_n ? h->peer[0].flag : nullptr, has_s ? h->peer[1].flag : nullptr, h->seq);
+            heat_signal<<<1, 32, 0, h->stream>>>(has[0] ? h->peer[0].flag : nullptr, has[1] ? h->peer[1].flag : nullptr,
+                                                 has[2] ? h->peer[2].flag : nullptr, has[3] ? h->peer[3].flag : nullptr, h->seq);
             h->launches++;
             CK(cudaGetLastError());
         }
@@ -897,13 +939,13 @@ static int after_upload(heat_handle* h)
 static int upload_from(heat_handle* h, const void* src, cudaMemcpyKind kind)
 {
     if (!h || !src) return fail(HEAT_E_INVALID, "heat_upload: bad arguments");
-    if ((h->p.rank > 0 || h->p.rank < h->p.nranks - 1) && !h->connected && !h->external_halo)
+    if ((h->p.nranks > 1 || h->p.nranks_y > 1) && !h->connected && !h->external_halo)
         return fail(HEAT_E_STATE, "heat_upload: connect the strips first");
     CK(cudaSetDevice(h->p.device));
-    const float* rows = (const float*)src + (size_t)h->lo * h->p.ny;
+    const float* rows = (const float*)src + (size_t)h->lo * h->p.ny + h->lo_c;
     // C:197-198: the initial field goes into both buffers -- over PCIe once, the second copy on the device
     CK(cudaMemcpy2DAsync(h->buf[0], h->pitch * sizeof(float), rows, (size_t)h->p.ny * sizeof(float),
-                         (size_t)h->p.ny * sizeof(float), h->nloc, kind, h->stream));
+                         (size_t)h->nyloc * sizeof(float), h->nloc, kind, h->stream));
     CK(cudaMemcpyAsync(h->buf[1], h->buf[0], (size_t)h->nloc * h->pitch * sizeof(float), cudaMemcpyDeviceToDevice, h->stream));
     return after_upload(h);
 }
@@ -914,10 +956,11 @@ extern "C" int heat_upload_device(heat_handle* h, const void* d_full_grid) { ret
 extern "C" int heat_init_inidat(heat_handle* h)
 {
     if (!h) return fail(HEAT_E_INVALID, "heat_init_inidat: null handle");
-    if ((h->p.rank > 0 || h->p.rank < h->p.nranks - 1) && !h->connected && !h->external_halo)
+    if ((h->p.nranks > 1 || h->p.nranks_y > 1) && !h->connected && !h->external_halo)
         return fail(HEAT_E_STATE, "heat_init_inidat: connect the strips first");
     CK(cudaSetDevice(h->p.device));
-    heat_inidat_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(h->buf[0], h->buf[1], h->p.nx, h->p.ny, h->lo, h->nloc, h->pitch);
+    heat_inidat_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(h->buf[0], h->buf[1], h->p.nx, h->p.ny, h->lo, h->nloc, h->pitch,
+                                                               h->lo_c, h->nyloc);
     h->launches++;
     CK(cudaGetLastError());
     return after_upload(h);
@@ -927,11 +970,11 @@ extern "C" int heat_download(heat_handle* h, float* full_grid)
 {
     if (!h || !full_grid) return fail(HEAT_E_INVALID, "heat_download: bad arguments");
     CK(cudaSetDevice(h->p.device));
-    // only the rows this strip owns (ghost rows belong to the neighbours)
-    const int first = h->row0 - h->lo;
-    CK(cudaMemcpy2DAsync(full_grid + (size_t)h->row0 * h->p.ny, (size_t)h->p.ny * sizeof(float),
-                         h->buf[h->cur] + (size_t)first * h->pitch, h->pitch * sizeof(float),
-                         (size_t)h->p.ny * sizeof(float), h->rows_own, cudaMemcpyDeviceToHost, h->stream));
+    // only the rows and columns this block owns (ghost rows/columns belong to the neighbours)
+    const int first = h->row0 - h->lo, firstc = h->col0 - h->lo_c;
+    CK(cudaMemcpy2DAsync(full_grid + (size_t)h->row0 * h->p.ny + h->col0, (size_t)h->p.ny * sizeof(float),
+                         h->buf[h->cur] + (size_t)first * h->pitch + firstc, h->pitch * sizeof(float),
+                         (size_t)h->cols_own * sizeof(float), h->rows_own, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     return HEAT_OK;
 }
@@ -940,6 +983,7 @@ extern "C" int heat_download(heat_handle* h, float* full_grid)
 extern "C" int heat_upload_local(heat_handle* h, const float* local_rows)
 {
     if (!h || !local_rows) return fail(HEAT_E_INVALID, "heat_upload_local: bad arguments");
+    if (h->p.nranks_y > 1) return fail(HEAT_E_STATE, "heat_upload_local: row strips only (column blocks use heat_upload)");
     // same copy as heat_upload, whose source starts at the strip's first local row
     return upload_from(h, local_rows - (size_t)h->lo * h->p.ny, cudaMemcpyHostToDevice);
 }
@@ -947,6 +991,7 @@ extern "C" int heat_upload_local(heat_handle* h, const float* local_rows)
 extern "C" int heat_download_local(heat_handle* h, float* own_rows)
 {
     if (!h || !own_rows) return fail(HEAT_E_INVALID, "heat_download_local: bad arguments");
+    if (h->p.nranks_y > 1) return fail(HEAT_E_STATE, "heat_download_local: row strips only (column blocks use heat_download)");
     CK(cudaSetDevice(h->p.device));
     const int first = h->row0 - h->lo;
     CK(cudaMemcpy2DAsync(own_rows, (size_t)h->p.ny * sizeof(float), h->buf[h->cur] + (size_t)first * h->pitch,
@@ -970,7 +1015,8 @@ extern "C" int heat_device_view(heat_handle* h, int which, void** d_ptr, int64_t
 extern "C" int heat_solve(const heat_params* p, float* grid, int* updates_done, int* converged)
 {
     if (!grid) return fail(HEAT_E_INVALID, "heat_solve: null grid");
-    if (p && p->nranks != 1) return fail(HEAT_E_INVALID, "heat_solve: one strip only (use the handle API for strips)");
+    if (p && (p->nranks != 1 || p->nranks_y != 1))
+        return fail(HEAT_E_INVALID, "heat_solve: one strip only (use the handle API for strips)");
     const bool timing = env_int("HEAT_TIMING", 0) != 0;
     auto now = [] {
         struct timespec ts;
@@ -1005,6 +1051,8 @@ extern "C" int heat_solve_gpus(const heat_params* p, int ngpus, float* grid, int
     heat_handle* h[64] = {};
     heat_params q = *p;
     q.nranks = ngpus;
+    q.rank_y = 0;
+    q.nranks_y = 1;
     int rc = HEAT_OK;
     for (int r = 0; r < ngpus && !rc; r++) {
         q.rank = r;
@@ -1082,7 +1130,7 @@ extern "C" int heat_ipc_export(heat_handle* h, void* blob, size_t blob_bytes)
     CK(cudaSetDevice(h->p.device));
     ipc_blob b;
     memset(&b, 0, sizeof b);
-    memcpy(b.magic, "HEATIPC1", 8);
+    memcpy(b.magic, "HEATIPC2", 8);
     void* ptrs[3] = {h->buf[0], h->buf[1], h->flags};
     for (int k = 0; k < 3; k++) {
         CK(cudaIpcGetMemHandle(&b.mem[k], ptrs[k]));
@@ -1092,21 +1140,40 @@ extern "C" int heat_ipc_export(heat_handle* h, void* blob, size_t blob_bytes)
     b.nloc = h->nloc;
     b.rank = h->p.rank;
     b.nranks = h->p.nranks;
+    b.nyloc = h->nyloc;
+    b.rank_y = h->p.rank_y;
+    b.nranks_y = h->p.nranks_y;
     b.pitch = h->pitch;
     memset(blob, 0, blob_bytes);
     memcpy(blob, &b, sizeof b);
     return HEAT_OK;
 }
 
+// side: 0 north, 1 south, 2 west, 3 east.  Which block must sit there, and which of ITS flag slots is mine.
+static void neighbour_of(const heat_handle* h, int side, int* rank, int* rank_y, int* their_slot)
+{
+    *rank = h->p.rank + (side == 0 ? -1 : side == 1 ? 1 : 0);
+    *rank_y = h->p.rank_y + (side == 2 ? -1 : side == 3 ? 1 : 0);
+    *their_slot = side ^ 1; // I am their south if they are my north, their east if they are my west
+}
+
+static bool has_side(const heat_handle* h, int side)
+{
+    return side == 0 ? h->p.rank > 0 : side == 1 ? h->p.rank < h->p.nranks - 1 : side == 2 ? h->p.rank_y > 0 : h->p.rank_y < h->p.nranks_y - 1;
+}
+
 static int open_side(heat_handle* h, int side, const void* blob)
 {
     ipc_blob b;
     memcpy(&b, blob, sizeof b);
-    if (memcmp(b.magic, "HEATIPC1", 8) != 0) return fail(HEAT_E_INVALID, "heat_ipc_connect: not an export blob");
-    const int want = h->p.rank + (side == 0 ? -1 : 1);
-    if (b.rank != want || b.nranks != h->p.nranks || b.pitch != h->pitch)
-        return fail(HEAT_E_PEER, "heat_ipc_connect: blob is strip %d/%d pitch %lld, expected strip %d/%d pitch %lld", b.rank,
-                    b.nranks, (long long)b.pitch, want, h->p.nranks, (long long)h->pitch);
+    if (memcmp(b.magic, "HEATIPC2", 8) != 0) return fail(HEAT_E_INVALID, "heat_ipc_connect: not an export blob");
+    int want, want_y, slot;
+    neighbour_of(h, side, &want, &want_y, &slot);
+    // row neighbours share my columns (same pitch), column neighbours share my rows (same local row count)
+    const bool shape_ok = side < 2 ? (b.pitch == h->pitch && b.nyloc == h->nyloc) : (b.nloc == h->nloc);
+    if (b.rank != want || b.rank_y != want_y || b.nranks != h->p.nranks || b.nranks_y != h->p.nranks_y || !shape_ok)
+        return fail(HEAT_E_PEER, "heat_ipc_connect: blob is block (%d,%d) of %dx%d, expected (%d,%d) of %dx%d with a matching shape",
+                    b.rank, b.rank_y, b.nranks, b.nranks_y, want, want_y, h->p.nranks, h->p.nranks_y);
     void* base[3];
     for (int k = 0; k < 3; k++) {
         cudaError_t e = cudaIpcOpenMemHandle(&base[k], b.mem[k], cudaIpcMemLazyEnablePeerAccess);
@@ -1115,41 +1182,56 @@ static int open_side(heat_handle* h, int side, const void* blob)
     }
     h->peer[side].buf[0] = (float*)((char*)base[0] + b.offset[0]);
     h->peer[side].buf[1] = (float*)((char*)base[1] + b.offset[1]);
-    // the neighbour's slot for messages from its south side is [1], from its north side [0]
     unsigned long long* f = (unsigned long long*)((char*)base[2] + b.offset[2]);
-    h->peer[side].flag = (side == 0) ? &f[1] : &f[0];
+    h->peer[side].flag = &f[slot];
     h->peer[side].nloc = b.nloc;
+    h->peer[side].nyloc = b.nyloc;
+    h->peer[side].pitch = b.pitch;
+    return HEAT_OK;
+}
+
+extern "C" int heat_ipc_connect2d(heat_handle* h, const void* north_blob, const void* south_blob, const void* west_blob,
+                                  const void* east_blob)
+{
+    if (!h) return fail(HEAT_E_INVALID, "heat_ipc_connect: null handle");
+    const void* blobs[4] = {north_blob, south_blob, west_blob, east_blob};
+    for (int side = 0; side < 4; side++)
+        if (has_side(h, side) != (blobs[side] != nullptr))
+            return fail(HEAT_E_PEER, "heat_ipc_connect: block (%d,%d) of %dx%d %s a neighbour on side %d", h->p.rank, h->p.rank_y,
+                        h->p.nranks, h->p.nranks_y, has_side(h, side) ? "needs" : "has no", side);
+    CK(cudaSetDevice(h->p.device));
+    for (int side = 0; side < 4; side++)
+        if (blobs[side]) {
+            int rc = open_side(h, side, blobs[side]);
+            if (rc) return rc;
+        }
+    h->connected = true;
     return HEAT_OK;
 }
 
 extern "C" int heat_ipc_connect(heat_handle* h, const void* north_blob, const void* south_blob)
 {
-    if (!h) return fail(HEAT_E_INVALID, "heat_ipc_connect: null handle");
-    const bool has_n = h->p.rank > 0, has_s = h->p.rank < h->p.nranks - 1;
-    if (has_n != (north_blob != nullptr) || has_s != (south_blob != nullptr))
-        return fail(HEAT_E_PEER, "heat_ipc_connect: strip %d of %d needs north=%d south=%d", h->p.rank, h->p.nranks, has_n, has_s);
-    CK(cudaSetDevice(h->p.device));
-    int rc = HEAT_OK;
-    if (has_n) rc = open_side(h, 0, north_blob);
-    if (!rc && has_s) rc = open_side(h, 1, south_blob);
-    if (rc) return rc;
-    h->connected = true;
-    return HEAT_OK;
+    return heat_ipc_connect2d(h, north_blob, south_blob, nullptr, nullptr);
 }
 
-extern "C" int heat_connect_local(heat_handle* h, heat_handle* north, heat_handle* south)
+extern "C" int heat_connect_local2d(heat_handle* h, heat_handle* north, heat_handle* south, heat_handle* west, heat_handle* east)
 {
     if (!h) return fail(HEAT_E_INVALID, "heat_connect_local: null handle");
-    const bool has_n = h->p.rank > 0, has_s = h->p.rank < h->p.nranks - 1;
-    if (has_n != (north != nullptr) || has_s != (south != nullptr))
-        return fail(HEAT_E_PEER, "heat_connect_local: strip %d of %d needs north=%d south=%d", h->p.rank, h->p.nranks, has_n, has_s);
+    heat_handle* nb[4] = {north, south, west, east};
+    for (int side = 0; side < 4; side++)
+        if (has_side(h, side) != (nb[side] != nullptr))
+            return fail(HEAT_E_PEER, "heat_connect_local: block (%d,%d) of %dx%d %s a neighbour on side %d", h->p.rank, h->p.rank_y,
+                        h->p.nranks, h->p.nranks_y, has_side(h, side) ? "needs" : "has no", side);
     CK(cudaSetDevice(h->p.device));
-    heat_handle* nb[2] = {north, south};
-    for (int side = 0; side < 2; side++) {
+    for (int side = 0; side < 4; side++) {
         heat_handle* o = nb[side];
         if (!o) continue;
-        if (o->p.rank != h->p.rank + (side ? 1 : -1) || o->p.nranks != h->p.nranks || o->pitch != h->pitch)
-            return fail(HEAT_E_PEER, "heat_connect_local: neighbour on side %d is strip %d, not adjacent", side, o->p.rank);
+        int want, want_y, slot;
+        neighbour_of(h, side, &want, &want_y, &slot);
+        const bool shape_ok = side < 2 ? (o->pitch == h->pitch && o->nyloc == h->nyloc) : (o->nloc == h->nloc);
+        if (o->p.rank != want || o->p.rank_y != want_y || o->p.nranks != h->p.nranks || o->p.nranks_y != h->p.nranks_y || !shape_ok)
+            return fail(HEAT_E_PEER, "heat_connect_local: neighbour on side %d is block (%d,%d), not adjacent", side, o->p.rank,
+                        o->p.rank_y);
         if (o->p.device != h->p.device) {
             int can = 0;
             CK(cudaDeviceCanAccessPeer(&can, h->p.device, o->p.device));
@@ -1161,12 +1243,19 @@ extern "C" int heat_connect_local(heat_handle* h, heat_handle* north, heat_handl
         }
         h->peer[side].buf[0] = o->buf[0];
         h->peer[side].buf[1] = o->buf[1];
-        h->peer[side].flag = (side == 0) ? &o->flags[1] : &o->flags[0];
+        h->peer[side].flag = &o->flags[slot];
         h->peer[side].nloc = o->nloc;
+        h->peer[side].nyloc = o->nyloc;
+        h->peer[side].pitch = o->pitch;
         h->local_nb[side] = o;
     }
     h->connected = true;
     return HEAT_OK;
+}
+
+extern "C" int heat_connect_local(heat_handle* h, heat_handle* north, heat_handle* south)
+{
+    return heat_connect_local2d(h, north, south, nullptr, nullptr);
 }
 
 // ------------------------------------------------------------------ update + residual without any allocation

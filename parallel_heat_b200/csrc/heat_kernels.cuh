@@ -88,15 +88,15 @@ __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<floa
 // (float)(ix*(nx-ix-1)*iy*(ny-iy-1)) with the int32 wrap of the reference (M:320).
 // Local array = global rows [row_lo, row_lo+nloc); writes both buffers (C:197-198).
 __global__ void heat_inidat_kernel(float* __restrict__ a, float* __restrict__ b, int nx, int ny, int row_lo,
-                                   int nloc, int64_t pitch)
+                                   int nloc, int64_t pitch, int col_lo, int nyloc)
 {
     const int64_t total = (int64_t)nloc * pitch;
     for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
         const int lr = (int)(k / pitch);
-        const int iy = (int)(k - (int64_t)lr * pitch);
-        const int ix = row_lo + lr;
+        const int ly = (int)(k - (int64_t)lr * pitch);
+        const int ix = row_lo + lr, iy = col_lo + ly;
         float v = 0.0f;
-        if (iy < ny) {
+        if (ly < nyloc) {
             uint32_t p = (uint32_t)ix * (uint32_t)(nx - ix - 1) * (uint32_t)iy * (uint32_t)(ny - iy - 1);
             v = (float)(int32_t)p;
         }
@@ -152,17 +152,24 @@ heat_step_generic(const float* __restrict__ in, float* __restrict__ out, int nro
 // (they read ghost rows and store the neighbour's ghost rows) wait for the neighbour's flag,
 // interior tiles start at once; when the last of those edge CTAs is done, it raises the
 // neighbour's flag.  All pointers null = single strip / event-ordered strips: no code runs.
+// Sides: 0 = north (row above), 1 = south, 2 = west (column to the left), 3 = east.  Row strips use
+// 0 and 1 only; 2-D blocks (the reference's own topology, M:51-75) use all four.
 struct strip_sync {
-    const unsigned long long* wait_n; // my slot written by the north neighbour
-    const unsigned long long* wait_s;
-    unsigned long long wait_value;    // epoch the neighbours must have completed
-    unsigned long long* sig_n;        // the north neighbour's slot for me
-    unsigned long long* sig_s;
+    const unsigned long long* wait[4]; // my slots, each written by the neighbour on that side
+    unsigned long long wait_value;     // epoch the neighbours must have completed
+    unsigned long long* sig[4];        // the neighbours' slots for me
     unsigned long long sig_value;
-    unsigned* counters;               // [0] north-edge CTAs done, [1] south-edge CTAs done
-    unsigned count_n, count_s;        // how many CTAs touch the north / south neighbour
-    int* status;                      // raised when a wait times out
+    unsigned* counters;                // [4] edge CTAs done, per side
+    unsigned count[4];                 // how many CTAs touch the neighbour on each side
+    int* status;                       // raised when a wait times out
     unsigned long long timeout_ns;
+};
+
+// Column neighbours of a 2-D block: where my first / last owned column goes (one float per row).
+struct col_peers {
+    float* w;          // west neighbour's new buffer, element (local row 0, its last local column)
+    float* e;          // east neighbour's new buffer, element (local row 0, local column 0)
+    int64_t pitch_w, pitch_e;
 };
 
 __device__ __forceinline__ void spin_until(const unsigned long long* f, unsigned long long value,
@@ -188,34 +195,33 @@ __device__ __forceinline__ void spin_until(const unsigned long long* f, unsigned
     }
 }
 
-// all threads of the CTA call these (block barrier inside); edge_n/edge_s are CTA-uniform
-__device__ __forceinline__ void strip_wait(const strip_sync& sy, bool edge_n, bool edge_s)
+// all threads of the CTA call these (block barrier inside); the edge flags are CTA-uniform
+__device__ __forceinline__ void strip_wait(const strip_sync& sy, bool edge_n, bool edge_s, bool edge_w = false, bool edge_e = false)
 {
-    const bool wn = edge_n && sy.wait_n, ws = edge_s && sy.wait_s;
-    if (wn || ws) {
+    const bool e[4] = {edge_n && sy.wait[0], edge_s && sy.wait[1], edge_w && sy.wait[2], edge_e && sy.wait[3]};
+    if (e[0] || e[1] || e[2] || e[3]) {
         if (threadIdx.x == 0) {
-            if (wn) spin_until(sy.wait_n, sy.wait_value, sy.timeout_ns, sy.status);
-            if (ws) spin_until(sy.wait_s, sy.wait_value, sy.timeout_ns, sy.status);
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                if (e[k]) spin_until(sy.wait[k], sy.wait_value, sy.timeout_ns, sy.status);
         }
         __syncthreads();
     }
 }
 
-__device__ __forceinline__ void strip_signal(const strip_sync& sy, bool edge_n, bool edge_s)
+__device__ __forceinline__ void strip_signal(const strip_sync& sy, bool edge_n, bool edge_s, bool edge_w = false, bool edge_e = false)
 {
-    const bool sn = edge_n && sy.sig_n, ss = edge_s && sy.sig_s;
-    if (sn || ss) {
+    const bool e[4] = {edge_n && sy.sig[0], edge_s && sy.sig[1], edge_w && sy.sig[2], edge_e && sy.sig[3]};
+    if (e[0] || e[1] || e[2] || e[3]) {
         __syncthreads(); // every thread's stores (local and peer) are issued
         if (threadIdx.x == 0) {
             __threadfence_system();
-            if (sn && atomicAdd(&sy.counters[0], 1u) == sy.count_n - 1) {
-                sy.counters[0] = 0;
-                asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(sy.sig_n), "l"(sy.sig_value) : "memory");
-            }
-            if (ss && atomicAdd(&sy.counters[1], 1u) == sy.count_s - 1) {
-                sy.counters[1] = 0;
-                asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(sy.sig_s), "l"(sy.sig_value) : "memory");
-            }
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                if (e[k] && atomicAdd(&sy.counters[k], 1u) == sy.count[k] - 1) {
+                    sy.counters[k] = 0;
+                    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(sy.sig[k]), "l"(sy.sig_value) : "memory");
+                }
         }
     }
 }
@@ -246,13 +252,13 @@ __device__ __forceinline__ int tile_of_block(int by, int ntiles, int reverse)
 // Rows [row_lo, row_hi) are updated (rows row_lo-1 and row_hi must exist: ring or ghost).
 //   grid.x = ceil(pitch/4 / THREADS), grid.y = number of row tiles, block = THREADS
 //   reverse != 0 walks the tiles bottom-up (alternate sweeps re-use what is left in L2).
-template <int ARITH, bool RESID, int THREADS, int UNROLL, bool SYNC>
+template <int ARITH, bool RESID, int THREADS, int UNROLL, bool SYNC, bool COLS = false>
 // the plain single-strip update is held to 48 registers (40 warps per SM), the variants with the
 // residual or the strip flags to 56 (36 warps), the double-precision mode to 64
-__global__ void __launch_bounds__(THREADS, (ARITH == HEAT_ARITH_F64MIX ? 1024 : (SYNC || RESID) ? 1152 : 1280) / THREADS)
+__global__ void __launch_bounds__(THREADS, (ARITH == HEAT_ARITH_F64MIX ? 1024 : (SYNC || RESID || COLS) ? 1152 : 1280) / THREADS)
 heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo, int row_hi, int ny, int64_t pitch,
               int rows_per_tile, float cx, float cy, unsigned* __restrict__ resid, float* peer_n, float* peer_s,
-              int ghost, int reverse, strip_sync sy)
+              int ghost, int reverse, strip_sync sy, col_peers cp = col_peers{})
 {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -265,7 +271,9 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
     const int r1 = min(r0 + rows_per_tile, row_hi);
     // tiles that touch a neighbour strip's data: they read ghost rows / store its ghost rows
     const bool edge_n = r0 < row_lo + ghost, edge_s = r1 > row_hi - ghost;
-    if (SYNC) strip_wait(sy, edge_n, edge_s);
+    // 2-D blocks: the first / last CTA of every tile row holds the column next to the west / east neighbour
+    const bool edge_w = COLS && blockIdx.x == 0, edge_e = COLS && blockIdx.x == gridDim.x - 1;
+    if (SYNC) strip_wait(sy, edge_n, edge_s, edge_w, edge_e);
 
     float m = 0.0f;
     // a whole warp beyond the row has nothing to do (warp-uniform, so the shuffles stay converged)
@@ -291,7 +299,8 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
 
     // Almost every warp takes this branch: no ring or padding column among its 128 columns, a full
     // tile, no neighbour strip's rows to store.  Same arithmetic, none of the special cases.
-    const bool plain_warp = __all_sync(FULL, live && !(kx || ky || kz || kw));
+    // (with column neighbours the float4 that ends at the last owned column is special too)
+    const bool plain_warp = __all_sync(FULL, live && !(kx || ky || kz || kw) && !(COLS && col + 3 == ny - 2));
     const bool plain_tile = (r1 - r0 == rows_per_tile) && (rows_per_tile % UNROLL == 0) && !(peer_n && edge_n) &&
                             !(peer_s && edge_s);
     if (plain_warp && plain_tile) {
@@ -357,7 +366,23 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
                 if (kz) o.z = c.z;
                 if (kw) o.w = c.w;
                 if (live) {
-                    st4(q, o);
+                    if (COLS && ((cp.w && col == 0) || (cp.e && col <= ny - 1 && ny - 1 < col + 4))) {
+                        // a ghost column lives in this float4: the neighbour stores it, I must not
+                        const bool gw = cp.w != nullptr, ge = cp.e != nullptr;
+                        if (!(gw && col == 0) && !(ge && col == ny - 1)) q[0] = o.x;
+                        if (!(ge && col + 1 == ny - 1)) q[1] = o.y;
+                        if (!(ge && col + 2 == ny - 1)) q[2] = o.z;
+                        if (!(ge && col + 3 == ny - 1)) q[3] = o.w;
+                        // my first owned column (local column 1) is the west neighbour's ghost column
+                        if (gw && col == 0) cp.w[(int64_t)(r + u) * cp.pitch_w] = o.y;
+                    } else {
+                        st4(q, o);
+                    }
+                    // my last owned column (local column ny-2) is the east neighbour's ghost column
+                    if (COLS && cp.e && col <= ny - 2 && ny - 2 < col + 4) {
+                        const int j = ny - 2 - col;
+                        cp.e[(int64_t)(r + u) * cp.pitch_e] = j == 0 ? o.x : j == 1 ? o.y : j == 2 ? o.z : o.w;
+                    }
                     // K3: the first / last `ghost` updated rows are the neighbours' ghost rows
                     if (peer_n && r + u < row_lo + ghost) st4(peer_n + (int64_t)(r + u - row_lo) * pitch + col, o);
                     if (peer_s && r + u >= row_hi - ghost) st4(peer_s + (int64_t)(r + u - (row_hi - ghost)) * pitch + col, o);
@@ -378,7 +403,7 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
     }
     } // warp inside the row
     if (RESID) block_max_to_global(live ? m : 0.0f, resid);
-    if (SYNC) strip_signal(sy, edge_n, edge_s);
+    if (SYNC) strip_signal(sy, edge_n, edge_s, edge_w, edge_e);
 }
 
 // ------------------------------------------------------------------ K4 temporal blocking
@@ -761,12 +786,15 @@ heat_absdiff_max(const float* __restrict__ a, const float* __restrict__ b, int r
 // ------------------------------------------------------------------ strip flags
 // After update u completes, a strip writes u+1 into each neighbour's flag slot
 // (system-scope release: its ghost-row stores are visible before the flag).
-__global__ void heat_signal(unsigned long long* peer_flag_n, unsigned long long* peer_flag_s, unsigned long long value)
+__global__ void heat_signal(unsigned long long* peer_flag_n, unsigned long long* peer_flag_s, unsigned long long* peer_flag_w,
+                            unsigned long long* peer_flag_e, unsigned long long value)
 {
     if (threadIdx.x == 0) {
         __threadfence_system();
-        if (peer_flag_n) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peer_flag_n), "l"(value) : "memory");
-        if (peer_flag_s) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peer_flag_s), "l"(value) : "memory");
+        unsigned long long* f[4] = {peer_flag_n, peer_flag_s, peer_flag_w, peer_flag_e};
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            if (f[k]) asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f[k]), "l"(value) : "memory");
     }
 }
 

@@ -61,7 +61,9 @@ class StripSolver:
     very class with an oracle-backed stand-in; the product always uses the defaults.
     """
 
-    def __init__(self, nx, ny, *, group=None, device=None, halo="p2p", solver_cls=None, rows_cls=None, **params):
+    def __init__(self, nx, ny, *, group=None, device=None, halo="p2p", cols=1, solver_cls=None, rows_cls=None, **params):
+        """cols > 1: 2-D blocks, world = (world // cols) row blocks x cols column blocks (the reference's
+        cartesian topology, M:51-75); rank r is block (r // cols, r % cols).  halo='p2p' only."""
         import torch.distributed as dist
         self.dist = dist
         self.group = group
@@ -74,10 +76,19 @@ class StripSolver:
         if device is None:
             device = 0
         self.device = device
+        if cols < 1 or self.world % cols:
+            raise ValueError(f"{self.world} ranks cannot form blocks with {cols} columns")
+        if cols > 1 and halo != "p2p":
+            raise ValueError("2-D blocks move their ghost columns with peer stores only (halo='p2p')")
+        self.cols, self.gx = cols, self.world // cols
+        self.bx, self.by = divmod(self.rank, cols)
         cls = solver_cls or api.HeatSolver
-        self.solver = cls(nx, ny, rank=self.rank, nranks=self.world, device=device, **params)
-        self.row0, self.rows = api.strip_rows(nx, self.world, self.rank)
-        self.lo, self.hi = local_window(nx, self.world, self.rank)
+        if cols > 1:
+            params = dict(params, rank_y=self.by, nranks_y=cols)
+        self.solver = cls(nx, ny, rank=self.bx, nranks=self.gx, device=device, **params)
+        self.row0, self.rows = api.strip_rows(nx, self.gx, self.bx)
+        self.col0, self.ncols = api.strip_rows(ny, cols, self.by)
+        self.lo, self.hi = local_window(nx, self.gx, self.bx)
         self.nloc = self.hi - self.lo
         self.conv_every = int(self.solver.params.conv_every)
         self._rows = (rows_cls or _CudaRows)(self.solver)
@@ -93,14 +104,19 @@ class StripSolver:
                 self.solver.set_stream(torch.cuda.current_stream(device).cuda_stream)
         if self.world > 1:
             self.solver.set_allreduce_max(self._allreduce_max)
+        self.halo = self.halo if self.world > 1 else "none"
 
     # ------------------------------------------------------------------ wiring
     def _connect_p2p(self):
         blobs = [None] * self.world
         self.dist.all_gather_object(blobs, self.solver.ipc_export(), group=self.group)
-        north = blobs[self.rank - 1] if self.rank > 0 else None
-        south = blobs[self.rank + 1] if self.rank < self.world - 1 else None
-        self.solver.ipc_connect(north, south)
+        def at(bx, by):
+            return blobs[bx * self.cols + by] if 0 <= bx < self.gx and 0 <= by < self.cols else None
+        if self.cols > 1:
+            self.solver.ipc_connect(at(self.bx - 1, self.by), at(self.bx + 1, self.by), at(self.bx, self.by - 1),
+                                    at(self.bx, self.by + 1))
+        else:
+            self.solver.ipc_connect(at(self.bx - 1, 0), at(self.bx + 1, 0))
         self.dist.barrier(group=self.group)
 
     def _allreduce_max(self, value):
@@ -174,14 +190,14 @@ class StripSolver:
         """Newest field assembled on rank `dst` (replaces the END messages, M:270-297)."""
         mine = np.zeros((self.nx, self.ny), np.float32)
         self.solver.download(mine)
-        part = np.ascontiguousarray(mine[self.row0:self.row0 + self.rows])
+        part = np.ascontiguousarray(mine[self.row0:self.row0 + self.rows, self.col0:self.col0 + self.ncols])
         if self.world == 1:
             return mine
         parts = [None] * self.world if self.rank == dst else None
         self.dist.gather_object(part, parts, dst=dst, group=self.group)
         if self.rank != dst:
             return None
-        return np.concatenate(parts, axis=0)
+        return np.concatenate([np.concatenate(parts[bx * self.cols:(bx + 1) * self.cols], axis=1) for bx in range(self.gx)], axis=0)
 
     def close(self):
         self.solver.close()

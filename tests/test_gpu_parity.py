@@ -544,3 +544,62 @@ def test_random_configurations_match_the_oracle(ph, oracle):
             got, done, conv = ph.solve(u, steps, temporal_block=T, **kw)
         assert (done, conv) == (wdone, wconv), (case, nx, ny, kw, T, g)
         assert_same_bits(got, want, f"case {case}: {nx}x{ny} steps={steps} T={T} strips={g} {kw}")
+
+
+# ---------------------------------------------------------------- 2-D blocks (the reference's topology, M:51-75)
+def run_blocks(ph, u, gx, gy, steps, **params):
+    nx, ny = u.shape
+    bs = {(i, j): ph.HeatSolver(nx, ny, rank=i, nranks=gx, rank_y=j, nranks_y=gy, **params) for i in range(gx) for j in range(gy)}
+    try:
+        for (i, j), b in bs.items():
+            b.connect_local(bs.get((i - 1, j)), bs.get((i + 1, j)), bs.get((i, j - 1)), bs.get((i, j + 1)))
+        for b in bs.values():
+            b.upload(u)
+        done, conv = ph.group_run(list(bs.values()), steps)
+        out = np.full_like(u, np.nan)
+        for b in bs.values():
+            b.download(out)
+        return out, done, conv
+    finally:
+        for b in bs.values():
+            b.close()
+
+
+@pytest.mark.parametrize("arith", MODES)
+@pytest.mark.parametrize("gx,gy", [(1, 2), (2, 2), (1, 3), (3, 2), (2, 4), (4, 1)])
+def test_block_decomposition_is_bit_identical(ph, oracle, gx, gy, arith):
+    # every block sees the same operands in the same order as the undecomposed run (SURVEY 8(e) invariant)
+    for shape in [(24, 24), (67, 130), (40, 517), (130, 1030), (36, 2052)]:
+        u = field(shape, seed=gx * 10 + gy)
+        want, _, _ = oracle.solve(u, 21, arith=arith)
+        got, done, _ = run_blocks(ph, u, gx, gy, 21, arith=arith)
+        assert done == 21
+        assert_same_bits(got, want, f"{gx}x{gy} blocks {shape} arith={arith}")
+
+
+def test_blocks_convergence_and_inidat(ph, oracle):
+    u = ph.inidat(40, 48)
+    want, wdone, wconv = oracle.solve(u, 100000, arith=2, conv_every=20, conv_phase=0, step_convention=1)
+    got, done, conv = run_blocks(ph, u, 2, 3, 100000, arith=2, conv_every=20, conv_phase=0, step_convention=1)
+    assert wconv and conv and done == wdone
+    assert_same_bits(got, want)
+    # device-side inidat of a block = the block's window of the host inidat
+    bs = {(i, j): ph.HeatSolver(70, 90, rank=i, nranks=2, rank_y=j, nranks_y=2) for i in range(2) for j in range(2)}
+    try:
+        for (i, j), b in bs.items():
+            b.connect_local(bs.get((i - 1, j)), bs.get((i + 1, j)), bs.get((i, j - 1)), bs.get((i, j + 1)))
+        for b in bs.values():
+            b.init_inidat()
+        out = np.zeros((70, 90), np.float32)
+        ph.group_run(list(bs.values()), 5)
+        for b in bs.values():
+            b.download(out)
+    finally:
+        for b in bs.values():
+            b.close()
+    assert_same_bits(out, oracle.solve(oracle.inidat(70, 90), 5, arith=0)[0])
+
+
+def test_blocks_refuse_temporal_blocking(ph):
+    with pytest.raises(ph.HeatError):
+        ph.HeatSolver(64, 64, rank_y=0, nranks_y=2, temporal_block=2)

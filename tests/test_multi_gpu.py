@@ -29,7 +29,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, shape, steps, halo, params, out_path):
+def _worker(rank, world, port, shape, steps, halo, params, out_path, cols=1):
     sys.path.insert(0, str(ROOT))
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     rdzv = "file://" + out_path + ".rdzv"  # a file store: no TCP port to collide on
@@ -41,7 +41,7 @@ def _worker(rank, world, port, shape, steps, halo, params, out_path):
         import parallel_heat_b200 as ph
         from parallel_heat_b200.strips import StripSolver
         u = ph.inidat(*shape) if params.pop("inidat", True) else None
-        s = StripSolver(shape[0], shape[1], device=rank, halo=halo, **params)
+        s = StripSolver(shape[0], shape[1], device=rank, halo=halo, cols=cols, **params)
         s.upload(u)
         done, conv = s.run(steps)
         full = s.gather(0)
@@ -103,3 +103,25 @@ def test_solve_gpus_one_shot(ph, oracle):
                                     step_convention=ph.STEPS_MPI, temporal_block=2)
     assert (done, conv) == (wdone, wconv)
     assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+@needs2
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("shape,steps,params", [
+    ((64, 64), 50, dict(arith=0)),
+    ((257, 1030), 33, dict(arith=1)),
+    ((40, 48), 100000, dict(arith=2, step_convention=1, conv_every=20, conv_phase=0)),
+])
+def test_blocks_one_process_per_gpu(tmp_path, oracle, ph, shape, steps, params):
+    # column blocks across processes: ghost columns by peer stores, four flags per block
+    import torch.multiprocessing as mp
+    world = 4 if ngpus() >= 4 else 2
+    cols = 2
+    out = tmp_path / "out.npz"
+    mp.spawn(_worker, args=(world, _free_port(), shape, steps, "p2p", dict(params), str(out), cols), nprocs=world, join=True)
+    r = np.load(out)
+    want, wdone, wconv = oracle.solve(oracle.inidat(*shape), steps, arith=params.get("arith", 0),
+                                      step_convention=params.get("step_convention", 0),
+                                      conv_every=params.get("conv_every", 0), conv_phase=params.get("conv_phase", 1))
+    assert (int(r["done"]), bool(r["conv"])) == (wdone, wconv)
+    assert np.array_equal(r["full"].view(np.uint32), want.view(np.uint32))
