@@ -10,7 +10,7 @@ dump() { # $1 = substring of the mangled name, $2 = output
   echo "# instruction mix" >> "$2"
   grep -E '^\s+/\*[0-9a-f]{4}\*/' "$2" | awk '{print $2}' | sed 's/\..*//;s/;//' | sort | uniq -c | sort -rn | head -25 | sed 's/^/# /' >> "$2"
 }
-dump "heat_step_vecILi0ELb0ELi128ELi4ELb0" profiles/sass_heat_step_vec_fma.txt
-dump "heat_step_vecILi0ELb1ELi128ELi4ELb0" profiles/sass_heat_step_vec_fma_residual.txt
+dump "heat_step_vecILi0ELb0ELi128ELi4ELb0ELb0" profiles/sass_heat_step_vec_fma.txt
+dump "heat_step_vecILi0ELb1ELi128ELi4ELb0ELb0" profiles/sass_heat_step_vec_fma_residual.txt
 dump "heat_step_tbILi0ELi4ELi1ELb0" profiles/sass_heat_step_tb_fma_T4.txt
 grep -cE "UTMALDG|UBLKCP|LDG.E.128|STG.E.128|SHFL|REDUX" profiles/sass_heat_step_vec_fma_residual.txt || true
