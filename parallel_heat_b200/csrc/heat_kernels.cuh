@@ -215,11 +215,17 @@ __device__ __forceinline__ void strip_signal(const strip_sync& sy, bool edge_n, 
     if (e[0] || e[1] || e[2] || e[3]) {
         __syncthreads(); // every thread's stores (local and peer) are issued
         if (threadIdx.x == 0) {
-            __threadfence_system();
+            // Row neighbours: a handful of edge CTAs, each fences at system scope before it counts itself.
+            // Column neighbours: one edge CTA per tile row (thousands); they fence at GPU scope only and the
+            // CTA that arrives last issues the one system-scope fence -- the release is cumulative over the
+            // arrivals it observed through the counter (8 GPUs, 2x4 blocks: 1.07 -> see DESIGN.md ms per pass).
+            if (e[0] || e[1]) __threadfence_system();
+            else __threadfence();
 #pragma unroll
             for (int k = 0; k < 4; k++)
                 if (e[k] && atomicAdd(&sy.counters[k], 1u) == sy.count[k] - 1) {
                     sy.counters[k] = 0;
+                    if (k >= 2) __threadfence_system();
                     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(sy.sig[k]), "l"(sy.sig_value) : "memory");
                 }
         }
