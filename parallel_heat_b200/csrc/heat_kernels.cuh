@@ -218,7 +218,7 @@ __device__ __forceinline__ void strip_signal(const strip_sync& sy, bool edge_n, 
             // Row neighbours: a handful of edge CTAs, each fences at system scope before it counts itself.
             // Column neighbours: one edge CTA per tile row (thousands); they fence at GPU scope only and the
             // CTA that arrives last issues the one system-scope fence -- the release is cumulative over the
-            // arrivals it observed through the counter (8 GPUs, 2x4 blocks: 1.07 -> see DESIGN.md ms per pass).
+            // arrivals it observed through the counter.
             if (e[0] || e[1]) __threadfence_system();
             else __threadfence();
 #pragma unroll
