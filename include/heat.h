@@ -102,7 +102,8 @@ int heat_create(const heat_params *p, heat_handle **out);
 int heat_destroy(heat_handle *h);
 /* Use the caller's CUDA stream (a cudaStream_t passed as void*) instead of the handle's own. */
 int heat_set_stream(heat_handle *h, void *cuda_stream);
-/* Host -> device of the FULL nx*ny field into BOTH buffers (C:197-198); a strip takes its rows. */
+/* Host -> device of the FULL nx*ny field into BOTH buffers (C:197-198); a strip takes its rows
+ * (ghost rows included), a 2-D block its rows x columns window (ghost columns included). */
 int heat_upload(heat_handle *h, const float *full_grid);
 /* Same from a device pointer holding the full field (used when the field is already in HBM). */
 int heat_upload_device(heat_handle *h, const void *d_full_grid);
@@ -123,15 +124,18 @@ int heat_sync(heat_handle *h);
 int heat_elapsed_ms(heat_handle *h, float *ms);
 /* max |old-new| over this strip for the most recent update (runs one reduction pass). */
 int heat_residual(heat_handle *h, float *residual);
-/* Newest field -> host; a strip writes only the rows it owns into full_grid. */
+/* Newest field -> host; a strip writes only the rows (a 2-D block: rows x columns) it owns into
+ * full_grid, so every rank of a job may download into the same array. */
 int heat_download(heat_handle *h, float *full_grid);
 /* The same for a rank that holds only its strip: local_rows = the strip's window, dense
  * local_rows x ny (global rows first_global_row ..., ghost rows included: see heat_device_view);
- * own_rows receives the rows the strip owns (heat_strip_rows), dense. */
+ * own_rows receives the rows the strip owns (heat_strip_rows), dense.  Row strips only:
+ * HEAT_E_STATE for a handle with nranks_y > 1 (column blocks go through heat_upload/heat_download). */
 int heat_upload_local(heat_handle *h, const float *local_rows);
 int heat_download_local(heat_handle *h, float *own_rows);
 /* Device pointer / pitch (in floats) / local row count of the newest (which=0) or older
- * (which=1) buffer, and the global row of local row 0. */
+ * (which=1) buffer, and the global row of local row 0.  For a 2-D block the pointer is the block's
+ * first local column (its west ghost column when it has a west neighbour). */
 int heat_device_view(heat_handle *h, int which, void **d_ptr, int64_t *pitch, int *local_rows, int *first_global_row);
 /* Kernels launched by this handle so far (benchmarks report it). */
 int heat_launch_count(heat_handle *h, int64_t *launches);
@@ -164,9 +168,10 @@ int heat_step_residual_noalloc(const void *d_in, void *d_out, int nx, int ny, fl
 
 /* ---- row strips across GPUs (replaces the 2-D block topology + persistent halo requests,
  *      M:51-84,130-155,160-161,177,263) --------------------------------------------------
- * Strip r of n owns global rows [row0, row0+rows).  Each strip keeps one ghost row per
- * neighbour; after every update a strip stores its first/last owned row straight into the
- * neighbour's ghost row over NVLink and then raises the neighbour's step flag. */
+ * Strip r of n owns global rows [row0, row0+rows).  Each strip keeps T = temporal_block ghost rows
+ * per neighbour; in every pass (T updates) the update kernel stores the strip's first/last T owned
+ * rows straight into the neighbour's ghost rows over NVLink and raises the neighbour's step flag;
+ * only the CTAs that touch a neighbour's rows ever wait for a flag. */
 int heat_strip_rows(int nx, int nranks, int rank, int *row0, int *rows);
 /* Who moves the ghost rows: HEAT_HALO_P2P (default) = the update kernel stores them into the
  * connected neighbours; HEAT_HALO_EXTERNAL = the caller copies row 1 / row n-2 of the newest
