@@ -75,7 +75,9 @@ int heat_device_count(void);
  * best): HEAT_ROWS_PER_TILE (K1/K2 tile height, 8), HEAT_ROWS_PER_TILE_TB (K4 tile height, by row length),
  * HEAT_SERPENTINE (alternate sweep direction, 1), HEAT_GRAPHS (CUDA graphs of 16 passes, 1),
  * HEAT_RESIDENT (field resident in shared memory for grids that fit, 1), HEAT_RESIDENT_G (updates per
- * neighbour exchange of that kernel, 6), HEAT_TIMING (heat_solve prints its phases to stderr, 0). */
+ * neighbour exchange of that kernel, 6), HEAT_TIMING (heat_solve prints its phases to stderr, 0),
+ * HEAT_COLS_FIRST (2-D blocks across processes: M > 0 hands the column-edge CTAs out first, M tile rows
+ * each; 0 = grid order, the default -- bit-identical either way, slower on 2 GPUs, kept for the 2x4 study). */
 
 /* ---- the reference's helpers, same arguments (M:315-341, C:274-300) ------------------ */
 /* inidat: u[ix*ny+iy] = (float)(ix*(nx-ix-1)*iy*(ny-iy-1)) in wrapping int32 (M:320). */

@@ -198,6 +198,7 @@ struct heat_handle {
     heat_handle* local_nb[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev_done[2] = {nullptr, nullptr}; // recorded after epoch e in ev_done[e & 1]
     bool serpentine = true;
+    int cols_first = 0; // HEAT_COLS_FIRST = M: column-edge CTAs ahead of the rest, M tile rows each (2-D blocks across processes)
     // CUDA graphs of GRAPH_PASSES consecutive passes, one per (newest buffer, sweep direction, fused?)
     cudaGraphExec_t graphs[2][2][2] = {};
     cudaStream_t capture_stream = nullptr;
@@ -357,6 +358,8 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     h->rows_per_tile = env_int("HEAT_ROWS_PER_TILE", 0);
     h->rows_per_tile_tb = env_int("HEAT_ROWS_PER_TILE_TB", 0);
     h->serpentine = env_int("HEAT_SERPENTINE", 1) != 0;
+    h->cols_first = env_int("HEAT_COLS_FIRST", 0);
+    if (h->cols_first < 0) h->cols_first = 0;
 #ifdef HEAT_BOUNDS_CHECK
     h->use_graphs = false; // the debug build synchronises around every pass
     h->use_resident = false;
@@ -420,6 +423,10 @@ static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, fl
     dim3 grid((unsigned)((h->pitch / 4 + THREADS - 1) / THREADS), (unsigned)((rows + rpt - 1) / rpt));
     count_edge_ctas(h, rows, rpt, grid.x, grid.y);
     if (h->p.nranks_y > 1) { // 2-D blocks: column neighbours too
+        const int M = h->col_args.edge_first, xe = ((ny - 2) >> 2) / THREADS;
+        if (M > 1 && h->sync_args.counters && cols_first_active((int)grid.x, (int)grid.y, xe))
+            // column-edge CTAs team up M tile rows at a time (the two row-edge tile rows stay as they are)
+            h->sync_args.count[2] = h->sync_args.count[3] = 2 + (grid.y - 2 + M - 1) / M;
         if (h->sync_args.counters)
             heat_step_vec<ARITH, RESID, THREADS, UNROLL, true, true><<<grid, THREADS, 0, h->stream>>>(
                 in, out, h->upd_lo, h->upd_hi, ny, h->pitch, rpt, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse,
@@ -534,6 +541,7 @@ static int enqueue_update(heat_handle* h, bool resid, int fused = 1)
     float* out = h->buf[1 - h->cur];
     float *pn = nullptr, *ps = nullptr;
     h->col_args = col_peers{};
+    h->col_args.edge_first = h->cols_first;
     if (strips) {
         if (local) {
             // neighbour's epoch `seq` (its previous update, or its upload) must be complete

@@ -170,6 +170,8 @@ struct col_peers {
     float* w;          // west neighbour's new buffer, element (local row 0, its last local column)
     float* e;          // east neighbour's new buffer, element (local row 0, local column 0)
     int64_t pitch_w, pitch_e;
+    int edge_first;    // HEAT_COLS_FIRST = M > 0: column-edge CTAs are handed out before the rest of the block and
+                       // each covers M tile rows (see cols_first); 0 = plain grid order
 };
 
 __device__ __forceinline__ void spin_until(const unsigned long long* f, unsigned long long value,
@@ -248,6 +250,33 @@ __device__ __forceinline__ int tile_of_block(int by, int ntiles, int reverse)
     return reverse ? (ntiles - 1 - by) : by;
 }
 
+// 2-D blocks with step flags, optional order (HEAT_COLS_FIRST=1): every tile row has one CTA next to the west
+// and one next to the east neighbour, so in grid order the last of them finishes with the pass and the
+// neighbours' flags travel while the next pass already waits for them.  This remaps (bx, by) so that after the
+// two row-edge tile rows (by = 0, 1: unchanged) the 2*(gy-2) column-edge CTAs of the other tile rows come next,
+// then everything else row by row.  A permutation of the grid; `xe` is the east-edge CTA column.
+// Returns false when the grid is too small for it (the host applies the same test, see cols_first_active).
+__host__ __device__ __forceinline__ bool cols_first_active(int gx, int gy, int xe) { return gy > 2 && gx > 2 && xe > 0; }
+__device__ __forceinline__ bool cols_first(int& bx, int& by, int gx, int gy, int xe)
+{
+    if (!cols_first_active(gx, gy, xe)) return false;
+    int b = by * gx + bx - 2 * gx;
+    if (b < 0) return true;
+    const int rows = gy - 2;
+    if (b < 2 * rows) {
+        by = 2 + (b >> 1);
+        bx = (b & 1) ? xe : 0;
+        return true;
+    }
+    b -= 2 * rows;
+    const int w = gx - 2;
+    by = 2 + b / w;
+    int k = 1 + b % w; // 1 .. gx-2, stepping over xe
+    if (k >= xe) k++;
+    bx = k;
+    return true;
+}
+
 // ------------------------------------------------------------------ K1/K2 vector row streaming
 // Each thread owns 4 consecutive columns (one float4) and walks down `rows_per_tile`
 // rows keeping the N / C / S rows in registers: per row one LDG.128, one STG.128, two
@@ -269,16 +298,35 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int npitch = (int)pitch;
-    int col = (blockIdx.x * THREADS + threadIdx.x) * 4;
+    int bx = (int)blockIdx.x, by = (int)blockIdx.y;
+    // the CTA column that holds local column ny-2, the one next to the east neighbour (see edge_e below)
+    const int xe = ((ny - 2) >> 2) / THREADS;
+    int span = 1; // row tiles this CTA covers
+    if (COLS && SYNC && cp.edge_first && cols_first(bx, by, (int)gridDim.x, (int)gridDim.y, xe)) {
+        // Every column-edge CTA ends with a fence behind its peer stores (an NVLink round trip during which it
+        // holds its slot).  With edge_first = M > 1 the column-edge CTAs of M consecutive tile rows team up: the
+        // first does the rows of all M, the others leave at once -- M times fewer fences, and since these CTAs
+        // were handed out first the long ones run beside the rest of the pass, not after it.
+        if (cp.edge_first > 1 && by >= 2 && (bx == 0 || bx == xe)) {
+            const int e = by - 2;
+            if (e % cp.edge_first) return;
+            span = min(cp.edge_first, (int)gridDim.y - 2 - e);
+        }
+    }
+    int col = (bx * THREADS + threadIdx.x) * 4;
 
     const int ntiles = gridDim.y;
-    const int tile = tile_of_block<SYNC>((int)blockIdx.y, ntiles, reverse);
+    int tile = tile_of_block<SYNC>(by, ntiles, reverse);
+    if (COLS && SYNC && span > 1 && reverse) tile -= span - 1; // bottom-up sweeps number the tiles downwards
     const int r0 = row_lo + tile * rows_per_tile;
-    const int r1 = min(r0 + rows_per_tile, row_hi);
+    const int r1 = min(r0 + span * rows_per_tile, row_hi);
     // tiles that touch a neighbour strip's data: they read ghost rows / store its ghost rows
     const bool edge_n = r0 < row_lo + ghost, edge_s = r1 > row_hi - ghost;
-    // 2-D blocks: the first / last CTA of every tile row holds the column next to the west / east neighbour
-    const bool edge_w = COLS && blockIdx.x == 0, edge_e = COLS && blockIdx.x == gridDim.x - 1;
+    // 2-D blocks: per tile row one CTA holds the column next to the west neighbour (local column 1) and one the
+    // column next to the east neighbour (local column ny-2: it reads the ghost column ny-1 and stores into the
+    // neighbour).  The latter is NOT always the last CTA of the row: the pitch is rounded up to 32 floats, so
+    // a trailing CTA of padding exists whenever ny-2 is the last column of a CTA (ny = 1 mod 4*THREADS).
+    const bool edge_w = COLS && bx == 0, edge_e = COLS && bx == xe;
     if (SYNC) strip_wait(sy, edge_n, edge_s, edge_w, edge_e);
 
     float m = 0.0f;
@@ -307,7 +355,7 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
     // tile, no neighbour strip's rows to store.  Same arithmetic, none of the special cases.
     // (with column neighbours the float4 that ends at the last owned column is special too)
     const bool plain_warp = __all_sync(FULL, live && !(kx || ky || kz || kw) && !(COLS && col + 3 == ny - 2));
-    const bool plain_tile = (r1 - r0 == rows_per_tile) && (rows_per_tile % UNROLL == 0) && !(peer_n && edge_n) &&
+    const bool plain_tile = (r1 - r0 == span * rows_per_tile) && (rows_per_tile % UNROLL == 0) && !(peer_n && edge_n) &&
                             !(peer_s && edge_s);
     if (plain_warp && plain_tile) {
         const bool el = (lane == 0) || (lane == 31);

@@ -32,6 +32,7 @@ def _free_port():
 def _worker(rank, world, port, shape, steps, halo, params, out_path, cols=1):
     sys.path.insert(0, str(ROOT))
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    os.environ["HEAT_COLS_FIRST"] = str(int(params.pop("cols_first", 0)))  # read by heat_create (0 = grid order)
     rdzv = "file://" + out_path + ".rdzv"  # a file store: no TCP port to collide on
     import torch
     import torch.distributed as dist
@@ -111,6 +112,14 @@ def test_solve_gpus_one_shot(ph, oracle):
     ((64, 64), 50, dict(arith=0)),
     ((257, 1030), 33, dict(arith=1)),
     ((40, 48), 100000, dict(arith=2, step_convention=1, conv_every=20, conv_phase=0)),
+    # 1024 columns in two blocks: the west block's last owned column ends a CTA and a CTA of padding follows it,
+    # so "the east-edge CTA" is not the last one of the tile row
+    ((130, 1024), 40, dict(arith=0)),
+    # HEAT_COLS_FIRST=M: column-edge CTAs first, M tile rows each (three CTA columns per block, with and
+    # without the padding CTA; M dividing the tile rows or not; both sweep directions)
+    ((130, 2048), 40, dict(arith=0, cols_first=1)),
+    ((300, 2052), 31, dict(arith=1, cols_first=3)),
+    ((517, 2048), 24, dict(arith=0, cols_first=8)),
 ])
 def test_blocks_one_process_per_gpu(tmp_path, oracle, ph, shape, steps, params):
     # column blocks across processes: ghost columns by peer stores, four flags per block
