@@ -188,11 +188,16 @@ class StripSolver:
     # ------------------------------------------------------------------ result
     def gather(self, dst=0):
         """Newest field assembled on rank `dst` (replaces the END messages, M:270-297)."""
-        mine = np.zeros((self.nx, self.ny), np.float32)
-        self.solver.download(mine)
-        part = np.ascontiguousarray(mine[self.row0:self.row0 + self.rows, self.col0:self.col0 + self.ncols])
         if self.world == 1:
-            return mine
+            return self.solver.download(np.zeros((self.nx, self.ny), np.float32))
+        if self.cols == 1:
+            # a row strip hands over its own rows only: no rank but `dst` ever holds the whole field
+            part = self.solver.download_local(np.empty((self.rows, self.ny), np.float32))
+        else:
+            mine = np.zeros((self.nx, self.ny), np.float32)
+            self.solver.download(mine)
+            part = np.ascontiguousarray(mine[self.row0:self.row0 + self.rows, self.col0:self.col0 + self.ncols])
+            del mine
         parts = [None] * self.world if self.rank == dst else None
         self.dist.gather_object(part, parts, dst=dst, group=self.group)
         if self.rank != dst:

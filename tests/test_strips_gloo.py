@@ -65,6 +65,11 @@ class OracleStrip:
         out[self.row0:self.row0 + self.rows] = self.buf[self.cur][first:first + self.rows]
         return out
 
+    def download_local(self, out):
+        first = self.row0 - self.lo
+        out[:] = self.buf[self.cur][first:first + self.rows]
+        return out
+
     def close(self):
         pass
 
