@@ -226,8 +226,8 @@ struct heat_handle {
     int rows_per_tile = 0;
     int rows_per_tile_tb = 0;     // 0 = choose per launch
     int sm_count = 148;
-    // neighbours: side 0 = north (lower rows), 1 = south
-    unsigned* d_edge_count = nullptr;    // [2] edge-CTA arrival counters of the fused strip ordering
+    // neighbours: side 0 = north (lower rows), 1 = south, 2 = west (lower columns), 3 = east
+    unsigned* d_edge_count = nullptr;    // [4] edge-CTA arrival counters of the fused strip ordering, per side
     strip_sync sync_args = {};           // filled per pass for flag-ordered strips, else all null
     col_peers col_args = {};             // 2-D blocks: where my first / last owned column goes
     unsigned long long* flags = nullptr; // [0] written by the north neighbour, [1] south, [2] west, [3] east
