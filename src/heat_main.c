@@ -8,7 +8,8 @@
  *   - inidat()/prtdat() with the reference's names and arguments (M:315-341)
  * and adds run-time options so one binary covers every size:
  *   heat [--style mpi|cuda] [--nx N] [--ny N] [--steps S] [--step K] [--converge]
- *        [--arith fma|nofma|f64mix] [--gpus G] [--no-dump] [--bin-dump]
+ *        [--arith fma|nofma|f64mix] [--gpus G] [--temporal-block T] [--no-dump] [--bin-dump]
+ * --temporal-block T (1..4): T updates per pass over HBM, same bits (heat.h: temporal_block)
  * --style mpi  : STEPS+1 updates, check when (it+1)%STEP==0, MPI_F64MIX arithmetic,
  *                initial_im.dat / final_im.dat, timer around setup+loop like M:88,298
  * --style cuda : STEPS updates, check when it%20==0, F32_FMA arithmetic,
@@ -64,7 +65,7 @@ static int die(const char *what)
 int main(int argc, char *argv[])
 {
     int nx = NXPROB, ny = NYPROB, steps = STEPS, step = STEP, converge = CONVERGE_DEFAULT;
-    int gpus = 1, dump = 1, bin_dump = 0, arith = -1;
+    int gpus = 1, dump = 1, bin_dump = 0, arith = -1, tblock = 1;
     const char *style = HEAT_STYLE;
     for (int i = 1; i < argc; i++) {
         const char *a = argv[i];
@@ -75,6 +76,7 @@ int main(int argc, char *argv[])
         else if (!strcmp(a, "--steps") && v) steps = atoi(argv[++i]);
         else if (!strcmp(a, "--step") && v) step = atoi(argv[++i]);
         else if (!strcmp(a, "--gpus") && v) gpus = atoi(argv[++i]);
+        else if (!strcmp(a, "--temporal-block") && v) tblock = atoi(argv[++i]);
         else if (!strcmp(a, "--style") && v) style = argv[++i];
         else if (!strcmp(a, "--converge")) converge = 1;
         else if (!strcmp(a, "--no-dump")) dump = 0;
@@ -84,7 +86,7 @@ int main(int argc, char *argv[])
             arith = !strcmp(m, "fma") ? HEAT_F32_FMA : !strcmp(m, "nofma") ? HEAT_F32_NOFMA : !strcmp(m, "f64mix") ? HEAT_MPI_F64MIX : -2;
         } else {
             fprintf(stderr, "usage: %s [--style mpi|cuda] [--nx N] [--ny N] [--size N] [--steps S] [--step K] [--converge]\n"
-                            "       [--arith fma|nofma|f64mix] [--gpus G] [--no-dump] [--bin-dump]\n", argv[0]);
+                            "       [--arith fma|nofma|f64mix] [--gpus G] [--temporal-block T] [--no-dump] [--bin-dump]\n", argv[0]);
             return 2;
         }
     }
@@ -104,6 +106,7 @@ int main(int argc, char *argv[])
     p.conv_phase = mpi_style ? HEAT_PHASE_MPI : HEAT_PHASE_CUDA;
     p.arith = arith >= 0 ? arith : (mpi_style ? HEAT_MPI_F64MIX : HEAT_F32_FMA);
     p.nranks = gpus;
+    p.temporal_block = tblock; /* heat_create rejects anything outside 1..4 */
 
     float *grid = (float *)malloc((size_t)nx * ny * sizeof(float));
     if (!grid) {
