@@ -10,7 +10,7 @@ Makefiles need mpicc and /opt/cuda, which this image does not have):
           -DNXPROB=.. -DNYPROB=.. -DSTEPS=heat_ref_steps_v -DSTEP=heat_ref_step_v
           [-DCONVERGE] [-fopenmp -DOMPCH -DTHREAD_COUNT=omp_get_max_threads()]
           <ref>.c oracle/refbuild/ref_shim.c -lm
-      mpi_stub/mpi.h is a single-rank MPI written for this repo (no MPI in the
+      mpi_stub/mpi.h is an MPI stand-in (1 rank, or $HEAT_REF_RANKS forked ranks) written for this repo (no MPI in the
       image); ref_shim.h makes STEPS/STEP run-time and captures prtdat's values.
       <opt> is "-O0" (as shipped: mpi/Makefile:2,13 has no -O) or
       "-O3 -fwrapv -ffp-contract=off" (the stronger CPU baseline).
@@ -86,6 +86,8 @@ DEFAULT_MPI = [
     # (nx, ny, conv, omp, opt)
     (20, 20, False, False, "O0"), (20, 20, False, False, "O3"), (20, 20, True, False, "O3"),
     (33, 47, False, False, "O3"), (64, 64, False, False, "O3"), (64, 64, False, True, "O3"),
+    # HEAT_REF_RANKS > 1 (the reference's own block decomposition): sizes that 2x1 .. 4x3 rank grids divide
+    (48, 60, False, False, "O3"), (48, 60, True, False, "O3"), (48, 60, False, True, "O3"),
     (256, 256, False, False, "O3"), (431, 431, True, False, "O3"),
     (1024, 1024, False, False, "O0"), (1024, 1024, False, False, "O3"), (1024, 1024, False, True, "O3"),
     (1024, 1024, True, True, "O3"),

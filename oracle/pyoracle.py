@@ -152,17 +152,20 @@ def ref_binary(kind, nx, ny, conv=False, omp=False, opt="O3", nofma=False):
 
 
 def run_reference(kind, nx, ny, steps, conv=False, omp=False, opt="O3", nofma=False, step=20,
-                  capture=True, text=False, threads=None, timeout=3600):
+                  capture=True, text=False, threads=None, ranks=1, timeout=3600):
     """Run a prebuilt reference binary in a scratch dir.  Returns a dict with
     stdout, wall seconds, loop_secs (MPI stub's loop stamp), converged_print (the
     number the program printed, or None) and -- if capture -- 'initial'/'final'
-    arrays with the exact float bits prtdat was handed."""
+    arrays with the exact float bits prtdat was handed.  ranks > 1 (MPI program only): the stand-in
+    forks that many processes, i.e. the reference's own 2-D block decomposition with its halo messages
+    (nx and ny must be divisible by the rank grid MPI_Dims_create picks, as the reference assumes, M:72-73)."""
     import time
     exe = ref_binary(kind, nx, ny, conv, omp, opt, nofma)
     if not exe.exists():
         raise FileNotFoundError(f"{exe} (run oracle/build_ref.py where /root/reference exists)")
     env = dict(os.environ, HEAT_REF_STEPS=str(steps), HEAT_REF_STEP=str(step),
-               HEAT_REF_BIN="1" if capture else "0", HEAT_REF_TEXT="1" if text else "0")
+               HEAT_REF_BIN="1" if capture else "0", HEAT_REF_TEXT="1" if text else "0",
+               HEAT_REF_RANKS=str(int(ranks)))
     if threads:
         env["OMP_NUM_THREADS"] = str(threads)
     tmp_root = "/dev/shm" if os.path.isdir("/dev/shm") else None

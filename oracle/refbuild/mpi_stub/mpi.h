@@ -1,14 +1,19 @@
 /*
- * mpi.h -- single-rank MPI stand-in, written for this repo (TEST INFRASTRUCTURE).
+ * mpi.h -- MPI stand-in, written for this repo (TEST INFRASTRUCTURE).
  *
  * The container and the GPU box have no MPI.  The reference's MPI program
  * (/root/reference/mpi/mpi_heat_improved_persistent_stat.c) is compiled
- * UNMODIFIED against this header by oracle/build_ref.py: one rank, a 1x1
- * cartesian grid, every neighbour MPI_PROC_NULL.  Jacobi with exact halos is
- * decomposition independent, so one rank produces the same bits as any rank
- * count.  Only the 20 entry points that file uses exist.  The bodies live in
- * ../ref_shim.c so that the first MPI_Startall / first MPI_Request_free can
- * time-stamp the solver loop (M:159-269) without touching the source.
+ * UNMODIFIED against this header by oracle/build_ref.py.  Only the 20 entry
+ * points that file uses exist; their bodies live in ../ref_shim.c:
+ *   - $HEAT_REF_RANKS unset or 1: one rank, a 1x1 cartesian grid, every
+ *     neighbour MPI_PROC_NULL (Jacobi with exact halos is decomposition
+ *     independent, so one rank produces the same bits as any rank count);
+ *   - $HEAT_REF_RANKS = N: N forked processes exchanging messages through
+ *     shared-memory rings -- the reference's own 2-D block decomposition, its
+ *     row_type / col_type halos, persistent requests and LAND allreduce run
+ *     as written ("shim, not real MPI": no network, one box).
+ * The first MPI_Startall / first MPI_Request_free time-stamp the solver loop
+ * (M:159-269) without touching the source.
  */
 #ifndef HEAT_MPI_STUB_H
 #define HEAT_MPI_STUB_H

@@ -154,3 +154,32 @@ def test_live_reference_binary_agrees(oracle):
     assert np.array_equal(bits(fin), bits(r2["final"]))
     r3 = oracle.run_reference("mpi", 20, 20, 10000, conv=True, step=20)
     assert r3["converged_print"] == 1979
+
+
+@pytest.mark.skipif(not have_reference_binaries(), reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("ranks", [2, 4, 6, 8, 12])
+def test_reference_in_its_own_block_decomposition(oracle, ranks):
+    """The unmodified MPI program run as `ranks` processes (HEAT_REF_RANKS: the stand-in forks them and carries
+    the messages through shared memory): MPI_Dims_create's rank grid (2x1, 2x2, 3x2, 4x2, 4x3), row_type /
+    col_type halos, persistent requests (M:51-84,130-155,160-177,263).  Same bits as the undecomposed oracle."""
+    r = oracle.run_reference("mpi", 48, 60, 57, ranks=ranks)
+    fin, done, _ = oracle.solve(oracle.inidat(48, 60), 57, arith=oracle.MPI_F64MIX, step_convention=1)
+    assert done == 58 and np.array_equal(bits(fin), bits(r["final"]))
+    assert np.array_equal(bits(oracle.inidat(48, 60)), bits(r["initial"]))
+    # the OpenMP team inside every rank (M:163, -DOMPCH) changes nothing either
+    r = oracle.run_reference("mpi", 48, 60, 57, ranks=ranks, omp=True, threads=2)
+    assert np.array_equal(bits(fin), bits(r["final"]))
+
+
+@pytest.mark.skipif(not have_reference_binaries(), reason="oracle/_ref not built (needs /root/reference)")
+def test_reference_ranks_convergence_and_baseline_config(oracle, golden):
+    # MPI_Allreduce(LAND) over 4 and 6 ranks (M:255): the same stop as one rank and as the oracle
+    assert oracle.run_reference("mpi", 20, 20, 10000, conv=True, ranks=4)["converged_print"] == 1979
+    r = oracle.run_reference("mpi", 48, 60, 100000, conv=True, ranks=6)
+    fin, done, conv = oracle.solve(oracle.inidat(48, 60), 100000, arith=oracle.MPI_F64MIX, step_convention=1,
+                                   conv_every=20, conv_phase=0)
+    assert conv and r["converged_print"] == done - 1 and np.array_equal(bits(fin), bits(r["final"]))
+    # BASELINE config[0]: 1024^2, 1000 steps, 4 ranks -- the text dump SURVEY section 8(c) pins
+    e = [x for x in golden["plain"] if x["nx"] == 1024 and x["steps"] == 1000][0]
+    r = oracle.run_reference("mpi", 1024, 1024, 1000, ranks=4, text=True, capture=False)
+    assert r["final_text_md5"] == e["final_text_md5"] == "e2c85256585896d5183a3006279cea23"
