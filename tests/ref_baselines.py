@@ -41,9 +41,15 @@ try:
     add("B1 mpi 1024^2 STEPS=1000 as shipped (-O0), 1 rank (stand-in)", **mpi(1024, 1024, 1000, opt="O0"))
     add("B1 mpi 1024^2 STEPS=1000 -O3, 1 rank (stand-in)", **mpi(1024, 1024, 1000, opt="O3"))
     add("B2 mpi 1024^2 STEPS=1000 -O3 -DOMPCH, 4 threads", **mpi(1024, 1024, 1000, omp=True, threads=4))
+    add("B2 mpi 1024^2 STEPS=1000 -O3, 4 ranks 2x2 (BASELINE config[0]; shared-memory stand-in, not real MPI)",
+        **mpi(1024, 1024, 1000, ranks=4))
+    add("B2 mpi 1024^2 STEPS=1000 as shipped (-O0), 4 ranks 2x2", **mpi(1024, 1024, 1000, ranks=4, opt="O0"))
     add("B2 mpi 1024^2 STEPS=1000 -O3 -DOMPCH, all threads", **mpi(1024, 1024, 1000, omp=True))
+    add("B2 mpi 1024^2 STEPS=1000 -O3, 16 ranks 4x4", **mpi(1024, 1024, 1000, ranks=16))
     add("B2 mpi 1024^2 -DCONVERGE -DSTEP=20 -O3 -DOMPCH, all threads", **mpi(1024, 1024, 1000, omp=True, conv=True))
     add("B3 mpi 8192^2 STEPS=100 -O3 -DOMPCH, all threads", **mpi(8192, 8192, 100, omp=True))
+    add("B3 mpi 8192^2 STEPS=100 -O3 -DOMPCH, 16 ranks 4x4 x 1 thread", **mpi(8192, 8192, 100, omp=True, ranks=16, threads=1))
+    add("B3 mpi 8192^2 STEPS=100 -O3 -DOMPCH, 4 ranks 2x2 x 4 threads", **mpi(8192, 8192, 100, omp=True, ranks=4, threads=4))
     add("B3 mpi 8192^2 STEPS=10 as shipped (-O0) -DOMPCH, all threads", **mpi(8192, 8192, 10, omp=True, opt="O0"))
     add("B3 mpi 16384^2 -DCONVERGE STEPS=40 -O3 -DOMPCH, all threads", **mpi(16384, 16384, 40, omp=True, conv=True))
     add("B4 cuda_heat 8192^2 STEPS=2000", **cuda(8192, 8192, 2000))
