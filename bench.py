@@ -159,7 +159,8 @@ def time_reference(O, wl, cores, loop_budget_secs, max_updates):
     best = None
     for ranks, threads in reference_layouts(nx, ny, cores):
         try:
-            probe = O.run_reference("mpi", nx, ny, 2, conv=conv, omp=True, opt="O3", capture=False, threads=threads, ranks=ranks)
+            probe = O.run_reference("mpi", nx, ny, 2, conv=conv, omp=True, opt="O3", capture=False, threads=threads, ranks=ranks,
+                                    timeout=900)
         except Exception:
             if ranks == 1:
                 raise

@@ -145,7 +145,7 @@ static double now(void)
 static double t_loop0 = 0, t_loop1 = 0;
 
 #define MAX_RANKS 64
-#define RING_BYTES ((uint64_t)8 << 20) /* per ordered pair; virtual until touched */
+#define RING_BYTES ((uint64_t)2 << 20) /* per ordered pair (the largest message is one row or column); virtual until touched */
 
 typedef struct {
     _Atomic uint64_t head; /* bytes ever written (producer) */
