@@ -5,7 +5,8 @@ Run in the build container (needs /root/reference for oracle/build_ref.py):
     python oracle/build_ref.py && python tests/golden/make_golden.py
 The reference has no tests and no golden vectors of its own (SURVEY.md section 4);
 these fixtures are outputs of its MPI program, compiled unmodified against the
-single-rank MPI stand-in, with the exact float bits prtdat() was handed.
+MPI stand-in (one rank; every even-sized case is run again as 4 ranks, 2x2 blocks, and
+must give the same bits), with the exact float bits prtdat() was handed.
 
 Files written:
   golden_small.npz   full final fields for the small cases (bit patterns)
@@ -53,12 +54,21 @@ def main():
             e["final_text_md5"] = r["final_text_md5"]
         if keep:
             arrays[f"final_{nx}x{ny}_s{steps}"] = r["final"].view(np.uint32)
+        if nx % 2 == 0 and ny % 2 == 0:
+            # the same program as 4 ranks (2x2 blocks, HEAT_REF_RANKS): its halo exchange must not change a bit
+            r4 = O.run_reference("mpi", nx, ny, steps, ranks=4)
+            assert sha(r4["final"]) == e["final_sha256"] and sha(r4["initial"]) == e["initial_sha256"], (nx, ny, steps)
+            e["ranks_checked"] = [1, 4]
         out["plain"].append(e)
         print(e)
     for nx, ny, steps, step in CONV:
         r = O.run_reference("mpi", nx, ny, steps, conv=True, step=step)
         e = {"nx": nx, "ny": ny, "steps": steps, "step": step, "printed": r["converged_print"],
              "final_sha256": sha(r["final"])}
+        if nx % 2 == 0 and ny % 2 == 0:
+            r4 = O.run_reference("mpi", nx, ny, steps, conv=True, step=step, ranks=4)
+            assert r4["converged_print"] == e["printed"] and sha(r4["final"]) == e["final_sha256"], (nx, ny, step)
+            e["ranks_checked"] = [1, 4]
         out["conv"].append(e)
         print(e)
     for n in CENTRES:
