@@ -6,21 +6,29 @@
 
 A bench "step" is ONE Jacobi update of the whole grid (one pass of the hot path).
 Workloads (BASELINE.json configs):
-    c2      (default)  8192 x 8192 float32, no convergence check; at N GPUs the grid is
-                       (8192*N) x 8192 cut into N row strips (weak scaling of config[1])
-    c3                 16384 x 16384 with the convergence check every 20 updates (1 GPU)
-    strong             65536 x 65536 row strips over N GPUs (config[3])
+    strong  (default)  65536 x 65536 float32 cut into N row strips (config[3]; at N=1 the whole grid on one GPU)
+    c3                 16384 x 16384 with the convergence check every 20 updates (config[2], 1 GPU)
+    c2                 8192 x 8192, no convergence check (config[1]); at N GPUs (8192*N) x 8192 in N strips
     weak32k            (32768*N) x 32768, temporal_block 4 (config[4])
     c1                 1024 x 1024 (config[0]'s grid; a parity case, here only for curiosity)
-`value` = LUPs of all ranks / device time (CUDA events on the launching stream, max over
-ranks), inputs resident in HBM.  `e2e` = the same through heat_solve() with HOST buffers
-(H2D + K updates + D2H inside the timed region).  --impl reference times the reference's own
-MPI program (oracle/_ref, unmodified source, OpenMP build, all host cores) on the same grid.
+At N=1 the default run also measures c3, c2, weak32k and the MPI arithmetic (`also`), each the same way.
+
+How a number is taken (every workload, every N):
+    W warm-up updates, then one untimed repetition of the timed call (K updates), device sync, barrier;
+    2 untimed updates so that flag-ordered neighbour strips are in lockstep; then R >= 7 repetitions of
+    K updates back to back, each between its own pair of CUDA events on the launching stream; per
+    repetition the MAX over ranks; `ms_per_step` = MEDIAN repetition / K.  Nothing but event records and
+    the K-update call sits between the first and the last event (the clock sampler and every lazily
+    built thing were started before the barrier).
+`value` = LUPs of all ranks / that time, inputs resident in HBM.  `e2e` = the same through heat_solve()
+with HOST buffers (H2D + K updates + D2H inside the timed region).  --impl reference times the
+reference's own MPI program (oracle/_ref, unmodified source, OpenMP build, all host cores).
 """
 from __future__ import annotations
 
 import argparse
 import json
+import math
 import os
 import sys
 import threading
@@ -32,24 +40,38 @@ sys.path.insert(0, str(ROOT))
 
 METRIC = "GLUP/s (5-point Jacobi lattice-point updates per second, solver loop)"
 BYTES_PER_LUP = 8.0  # float32 single-step: 4 B read + 4 B written per point-update
+MIN_REPS, MAX_REPS, TARGET_REGION_MS = 7, 200, 250.0
+LOCKSTEP_UPDATES = 2
+PARITY_UPDATES = 24
 
 
 def workload(name, n):
+    if name == "strong":
+        return dict(name=name, nx=65536, ny=65536, conv_every=0, temporal_block=1, scaling="strong",
+                    text=f"65536x65536 float32 inidat field over {n} row strip(s), no convergence check")
     if name == "c2":
-        return dict(nx=8192 * n, ny=8192, conv_every=0, temporal_block=1, scaling="weak",
+        return dict(name=name, nx=8192 * n, ny=8192, conv_every=0, temporal_block=1, scaling="weak",
                     text=f"{8192 * n}x8192 float32 inidat field, {n} row strip(s) of 8192 rows, no convergence check")
     if name == "c3":
-        return dict(nx=16384, ny=16384, conv_every=20, temporal_block=1, scaling="weak",
+        return dict(name=name, nx=16384, ny=16384, conv_every=20, temporal_block=1, scaling="weak",
                     text="16384x16384 float32 inidat field, convergence check every 20 updates")
-    if name == "strong":
-        return dict(nx=65536, ny=65536, conv_every=0, temporal_block=1, scaling="strong",
-                    text=f"65536x65536 float32 inidat field over {n} row strip(s)")
     if name == "weak32k":
-        return dict(nx=32768 * n, ny=32768, conv_every=0, temporal_block=4, scaling="weak",
+        return dict(name=name, nx=32768 * n, ny=32768, conv_every=0, temporal_block=4, scaling="weak",
                     text=f"{32768 * n}x32768 float32 inidat field, {n} strip(s), 4 updates per HBM pass")
     if name == "c1":
-        return dict(nx=1024, ny=1024, conv_every=0, temporal_block=1, scaling="weak", text="1024x1024 float32 inidat field")
+        return dict(name=name, nx=1024, ny=1024, conv_every=0, temporal_block=1, scaling="weak", text="1024x1024 float32 inidat field")
     raise SystemExit(f"unknown workload {name}")
+
+
+def config_of(wl, arith_name, world, halo, cols):
+    """The `config` object of a JSON line; both arms print the same keys."""
+    nx, ny = wl["nx"], wl["ny"]
+    return {"workload": wl["text"], "nx": nx, "ny": ny, "arith": arith_name,
+            "conv_every": wl["conv_every"], "temporal_block": wl["temporal_block"],
+            "halo": (halo if world > 1 else "none"),
+            "decomposition": (f"{world // cols}x{cols} blocks" if world > 1 else "single"),
+            "l2": f"working set {2 * nx * ny * 4 >> 20} MiB vs 126 MB L2: inputs larger than L2, no flush "
+                  "(consecutive updates ARE the workload)"}
 
 
 def measured_peak():
@@ -63,7 +85,7 @@ def measured_peak():
 
 
 def ncu_traffic(name):
-    """Per-launch DRAM bytes of the step kernel from the committed ncu capture, if any."""
+    """Per-launch DRAM bytes of a kernel from the committed ncu capture, if any (profiles/traffic.json)."""
     f = ROOT / "profiles" / "traffic.json"
     if f.exists():
         try:
@@ -82,11 +104,15 @@ def host_cores():
 
 
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    """nvidia-smi clocks/throttle reasons (through NVML) sampled every few ms by a thread that is started
+    BEFORE the warm-up; window() then keeps the samples that fall inside a timed region."""
 
-    def __init__(self, index=0, period=0.1):
+    NAMES = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+             "hw_power_brake_slowdown": 0x80, "sync_boost": 0x10, "applications_clocks_setting": 0x2}
+
+    def __init__(self, index=0, period=0.004):
         self.index, self.period = index, period
-        self.samples, self.reasons = [], set()
+        self.samples = []  # (host time, sm MHz, reasons bitmask, power W)
         self.max_mhz = None
         self._stop = threading.Event()
         self._t = None
@@ -102,13 +128,13 @@ class ClockSampler:
     def _once(self):
         nv = self.nv
         try:
-            self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+            mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
             r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-            names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
-                     "hw_power_brake_slowdown": 0x80, "sync_boost": 0x10, "applications_clocks_setting": 0x2}
-            for k, bit in names.items():
-                if r & bit:
-                    self.reasons.add(k)
+            try:
+                w = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
+            except Exception:
+                w = None
+            self.samples.append((time.perf_counter(), mhz, r, w))
         except Exception:
             pass
 
@@ -121,15 +147,28 @@ class ClockSampler:
         if self.nv:
             self._t = threading.Thread(target=self._loop, daemon=True)
             self._t.start()
+        return self
 
     def stop(self):
         if self._t:
-            self._once()
             self._stop.set()
             self._t.join()
-        s = sorted(self.samples)
-        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(s)}
+            self._t = None
+
+    def window(self, t0, t1):
+        """Summary of the samples taken in [t0, t1] (host clock); the nearest one if the region was too short."""
+        inside = [s for s in self.samples if t0 <= s[0] <= t1]
+        if not inside and self.samples:
+            mid = 0.5 * (t0 + t1)
+            inside = [min(self.samples, key=lambda s: abs(s[0] - mid))]
+        mhz = sorted(s[1] for s in inside)
+        bits = 0
+        for s in inside:
+            bits |= s[2]
+        watts = [s[3] for s in inside if s[3] is not None]
+        return {"sm_mhz": (mhz[len(mhz) // 2] if mhz else None), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(k for k, b in self.NAMES.items() if bits & b), "samples": len(inside),
+                "power_w_max": (max(watts) if watts else None)}
 
 
 # ------------------------------------------------------------------------------------ reference arm
@@ -152,10 +191,24 @@ def reference_layouts(nx, ny, cores):
     return outs
 
 
-def time_reference(O, wl, cores, loop_budget_secs, max_updates):
+def reference_grid(wl):
+    """The grid the unmodified reference program runs for a workload, and why if it is not the workload's own.
+    The program keeps 5 copies of the field in static/stack arrays (M:46,87,280), initialises it on one thread
+    and walks it column-wise twice in prtdat (M:326-341, one fprintf per value): at 65536^2 that is 80 GiB and
+    about ten minutes outside the loop, at 32768^2 20 GiB and two to three minutes.  Its loop speed does not
+    depend on the grid size once the field is far larger than the caches, so those workloads are timed on
+    16384 x 16384 (the largest grid whose whole program ends inside the time-box) and the line says so."""
+    nx, ny = wl["nx"], wl["ny"]
+    if nx * ny > 16384 * 16384 * 2 and wl["conv_every"] == 0:
+        return 16384, 16384, (f"reference timed on 16384x16384 instead of {nx}x{ny}: its setup (single-threaded inidat, two "
+                              "column-wise prtdat walks, 5 field copies in static/stack arrays) does not fit the time-box "
+                              "at that size; its loop GLUP/s is size-independent beyond the caches")
+    return nx, ny, None
+
+
+def time_reference(O, nx, ny, conv, cores, loop_budget_secs, max_updates):
     """Times the unmodified reference MPI program (oracle/_ref) on a bounded sample of the workload: every
     layout is probed with 3 updates, the fastest one runs the sample.  Returns (glups, updates, secs, text)."""
-    nx, ny, conv = wl["nx"], wl["ny"], wl["conv_every"] > 0
     probed = []
     for ranks, threads in reference_layouts(nx, ny, cores):
         try:
@@ -184,67 +237,370 @@ def time_reference(O, wl, cores, loop_budget_secs, max_updates):
     return (nx - 2) * (ny - 2) * updates / r["loop_secs"] / 1e9, updates, r["loop_secs"], text
 
 
+def reference_sample(wl, cores, loop_budget_secs, max_updates):
+    """(glups, updates, secs, kind, sample text, reference_workload note) for one workload on the host cores."""
+    os.environ["OMP_NUM_THREADS"] = str(cores)  # torchrun exports OMP_NUM_THREADS=1 to its workers
+    from oracle import pyoracle as O
+    nx, ny, note = reference_grid(wl)
+    conv = wl["conv_every"] > 0
+    exe = O.ref_binary("mpi", nx, ny, conv=conv, omp=True, opt="O3")
+    if exe.exists():
+        glups, updates, secs, sample = time_reference(O, nx, ny, conv, cores, loop_budget_secs, max_updates)
+        return glups, updates, secs, "reference", sample, note, (nx, ny), cores
+    # no prebuilt reference binary for this grid: the C restatement (oracle/heat_oracle.c), same arithmetic
+    if nx * ny > 16384 * 16384:
+        nx = ny = 16384
+        note = f"oracle port timed on 16384x16384 instead of {wl['nx']}x{wl['ny']} (bounded sample)"
+    ini = O.inidat(nx, ny)
+    t0 = time.perf_counter()
+    O.solve(ini, 2, arith=O.MPI_F64MIX)
+    per_update = max((time.perf_counter() - t0) / 2, 1e-6)
+    updates = int(max(3, min(max_updates, loop_budget_secs / per_update)))
+    t0 = time.perf_counter()
+    O.solve(ini, updates, arith=O.MPI_F64MIX)
+    secs = time.perf_counter() - t0
+    threads = O.threads()
+    glups = (nx - 2) * (ny - 2) * updates / secs / 1e9
+    sample = f"{updates} updates of {nx}x{ny}: oracle/heat_oracle.c (C restatement, MPI_F64MIX), {threads} OpenMP threads"
+    return glups, updates, secs, "port", sample, note, (nx, ny), threads
+
+
 def run_reference_arm(args, wl, rank, world):
     if rank != 0:
         return
     cores = host_cores()
-    os.environ["OMP_NUM_THREADS"] = str(cores)  # torchrun exports OMP_NUM_THREADS=1 to its workers
-    from oracle import pyoracle as O
-    nx, ny = wl["nx"], wl["ny"]
-    out = {"metric": METRIC, "unit": "GLUP/s", "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
-           "warmup": args.warmup, "higher_is_better": True, "scaling": wl["scaling"], "vs_baseline": None,
-           "dtype": "f32 grid, f64-mixed arithmetic (M:168-174)", "data": "synthetic",
-           "config": {"workload": wl["text"], "nx": nx, "ny": ny}}
-    exe = O.ref_binary("mpi", nx, ny, conv=wl["conv_every"] > 0, omp=True, opt="O3")
-    if exe.exists():
-        # bounded sample: about 20 s of loop time
-        glups, updates, secs, sample = time_reference(O, wl, cores, 20.0, args.steps + args.warmup)
-        kind = "reference"
-    else:
-        ini = O.inidat(nx, ny)
-        t0 = time.perf_counter()
-        O.solve(ini, 2, arith=O.MPI_F64MIX)
-        per_update = max((time.perf_counter() - t0) / 2, 1e-6)
-        updates = int(max(3, min(args.steps + args.warmup, 20.0 / per_update)))
-        t0 = time.perf_counter()
-        O.solve(ini, updates, arith=O.MPI_F64MIX)
-        secs, kind = time.perf_counter() - t0, "port"
-        cores = O.threads()
-        glups = (nx - 2) * (ny - 2) * updates / secs / 1e9
-        sample = f"{updates} updates of {nx}x{ny}: oracle/heat_oracle.c (C restatement, MPI_F64MIX), {cores} OpenMP threads"
-    out.update(value=glups, ms_per_step=secs / updates * 1e3,
-               cpu_baseline={"value": glups, "unit": "GLUP/s", "cores": cores, "kind": kind, "sample": sample},
-               e2e={"value": glups, "unit": "GLUP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
+    glups, updates, secs, kind, sample, note, (rnx, rny), used = reference_sample(wl, cores, 20.0, args.steps + max(args.warmup, 3))
+    cfg = config_of(wl, "MPI_F64MIX", 1, "none", 1)
+    if (rnx, rny) != (wl["nx"], wl["ny"]):
+        cfg["nx"], cfg["ny"] = rnx, rny
+    out = {"metric": METRIC, "value": glups, "unit": "GLUP/s", "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": secs / updates * 1e3, "higher_is_better": True, "scaling": wl["scaling"],
+           "vs_baseline": None, "dtype": "f32 grid, f64-mixed arithmetic (M:168-174)", "data": "synthetic", "config": cfg,
+           "reference_workload": note,
+           "cpu_baseline": {"value": glups, "unit": "GLUP/s", "cores": used, "kind": kind, "sample": sample},
+           "e2e": {"value": glups, "unit": "GLUP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(out), flush=True)
 
 
 # ------------------------------------------------------------------------------------ cpu baseline (rank 0, N=1)
 def cpu_baseline(wl):
     cores = host_cores()
-    os.environ["OMP_NUM_THREADS"] = str(cores)
-    from oracle import pyoracle as O
-    nx, ny = wl["nx"], wl["ny"]
-    lups = (nx - 2) * (ny - 2)
-    exe = O.ref_binary("mpi", nx, ny, conv=wl["conv_every"] > 0, omp=True, opt="O3")
     try:
-        if exe.exists():
-            glups, updates, secs, sample = time_reference(O, wl, cores, 15.0, 2000)
-            return {"value": glups, "unit": "GLUP/s", "cores": cores, "kind": "reference", "sample": sample}
-        ini = O.inidat(nx, ny)
-        t0 = time.perf_counter()
-        O.solve(ini, 2, arith=O.MPI_F64MIX)
-        updates = int(max(3, min(2000, 15.0 / max((time.perf_counter() - t0) / 2, 1e-6))))
-        t0 = time.perf_counter()
-        O.solve(ini, updates, arith=O.MPI_F64MIX)
-        return {"value": lups * updates / (time.perf_counter() - t0) / 1e9, "unit": "GLUP/s", "cores": O.threads(),
-                "kind": "port", "sample": f"{updates} updates of {nx}x{ny}, oracle/heat_oracle.c MPI_F64MIX"}
+        glups, updates, secs, kind, sample, note, _, used = reference_sample(wl, cores, 12.0, 2000)
+        if note:
+            sample += " [" + note + "]"
+        return {"value": glups, "unit": "GLUP/s", "cores": used, "kind": kind, "sample": sample}
     except Exception as e:  # a baseline that cannot run must not take the GPU number down with it
         return {"value": None, "unit": "GLUP/s", "cores": cores, "kind": "unavailable", "sample": repr(e)[:200]}
 
 
+def reference_cuda_leg(peak):
+    """The reference's own GPU program on this GPU (north_star: "... and the reference's own cuda_heat.cu"):
+    unmodified cuda/cuda_heat.cu built for sm_100a at its largest grid that the 1-GPU configs name (8192^2).
+    Its own timer stops without a device sync (C:239), so the loop time is wall(STEPS=S) - wall(STEPS=0)."""
+    try:
+        from oracle import pyoracle as O
+        nx = ny = 8192
+        if not O.ref_binary("cuda", nx, ny).exists():
+            return {"value": None, "note": "oracle/_ref/cuda_heat_8192x8192 not built"}
+        S = 400
+        r0 = O.run_reference("cuda", nx, ny, 0, capture=False, timeout=600)
+        r1 = O.run_reference("cuda", nx, ny, S, capture=False, timeout=600)
+        secs = max(r1["wall_secs"] - r0["wall_secs"], 1e-6)
+        v = (nx - 2) * (ny - 2) * S / secs / 1e9
+        return {"value": v, "unit": "GLUP/s", "ms_per_step": secs / S * 1e3, "steps": S, "frac": v * BYTES_PER_LUP / peak,
+                "note": "unmodified cuda/cuda_heat.cu (C:140-163 kernel, C:200-211 launch loop), nvcc -O2 sm_100a, 8192x8192, "
+                        f"wall(STEPS={S}) - wall(STEPS=0); a reported baseline, not a target"}
+    except Exception as e:
+        return {"value": None, "note": "reference cuda_heat leg failed: " + repr(e)[:160]}
+
+
 # ------------------------------------------------------------------------------------ our arm
-def run_ours(args, wl, rank, world, local_rank):
+class Ctx:
+    """What every measurement needs: torch, the process group, the stream, the clock sampler."""
+
+    def __init__(self, torch, dist, rank, world, local_rank, stream, clocks):
+        self.torch, self.dist, self.rank, self.world, self.local_rank = torch, dist, rank, world, local_rank
+        self.stream, self.clocks = stream, clocks
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+            self.torch.cuda.synchronize()
+
+
+def measure(ctx, enqueue, sync, K, W, reps=None, launch_count=lambda: 0):
+    """The timing scheme of the module docstring.  Returns a dict with the per-repetition times (max over ranks)."""
+    torch = ctx.torch
+    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+    enqueue(W)
+    w0, w1 = ev(), ev()
+    w0.record(ctx.stream)
+    enqueue(K)  # the timed call itself, once, untimed: every lazily built thing exists afterwards
+    w1.record(ctx.stream)
+    sync()
+    warm_ms = w0.elapsed_time(w1)
+    if ctx.world > 1:
+        t = torch.tensor([warm_ms], device="cuda")
+        ctx.dist.all_reduce(t, op=ctx.dist.ReduceOp.MAX)
+        warm_ms = float(t.item())
+    R = reps or int(min(MAX_REPS, max(MIN_REPS, math.ceil(TARGET_REGION_MS / max(warm_ms, 1e-3)))))
+    events = [ev() for _ in range(R + 1)]
+    ctx.barrier()
+    enqueue(LOCKSTEP_UPDATES)  # neighbours wait for each other's flags here, not inside the first repetition
+    n0 = launch_count()
+    t0 = time.perf_counter()
+    events[0].record(ctx.stream)
+    for r in range(R):
+        enqueue(K)
+        events[r + 1].record(ctx.stream)
+    sync()
+    t1 = time.perf_counter()
+    n1 = launch_count()
+    ctx.barrier()
+    mine = [events[r].elapsed_time(events[r + 1]) for r in range(R)]
+    per_rank_median = [sorted(mine)[R // 2]]
+    times = mine
+    if ctx.world > 1:
+        t = torch.tensor(mine, device="cuda", dtype=torch.float64)
+        ctx.dist.all_reduce(t, op=ctx.dist.ReduceOp.MAX)
+        times = [float(x) for x in t.tolist()]
+        g = torch.zeros(ctx.world, device="cuda", dtype=torch.float64)
+        g[ctx.rank] = per_rank_median[0]
+        ctx.dist.all_reduce(g)
+        per_rank_median = [float(x) for x in g.tolist()]
+    s = sorted(times)
+    return {"reps": R, "K": K, "median_ms": s[R // 2], "best_ms": s[0], "worst_ms": s[-1], "mean_ms": sum(times) / R,
+            "per_rank_median_ms": per_rank_median, "warm_rep_ms": warm_ms, "clocks": ctx.clocks.window(t0, t1),
+            "host_secs": t1 - t0, "launches": n1 - n0}
+
+
+def device_window(torch, ptr, pitch, r0, r1, c0, c1, device):
+    """Rows [r0, r1) x columns [c0, c1) of a strip's local device array, as numpy."""
+    class _Arr:
+        pass
+    a = _Arr()
+    a.__cuda_array_interface__ = {"shape": (r1 - r0, c1 - c0), "strides": (4 * pitch, 4), "typestr": "<f4", "version": 3,
+                                  "data": (ptr + 4 * (pitch * r0 + c0), False)}
+    return torch.as_tensor(a, device=f"cuda:{device}").cpu().numpy()
+
+
+def inidat_window(nx, ny, r0, r1, c0, c1):
+    """inidat (M:320, int32 wrap included) on a window of the global grid."""
     import numpy as np
+    ix = np.arange(r0, r1, dtype=np.uint32)[:, None]
+    iy = np.arange(c0, c1, dtype=np.uint32)[None, :]
+    prod = ix * (np.uint32(nx) - ix - np.uint32(1)) * iy * (np.uint32(ny) - iy - np.uint32(1))
+    return prod.view(np.int32).astype(np.float32)
+
+
+def parity_windows(ctx, wl, arith, view, updates, get):
+    """Bit-exact check of what the timed code path computes, outside the timed region.  After `updates` updates of
+    the inidat field a point depends only on initial values at most `updates` rows/columns away, so a small
+    window can be checked against the oracle run on the window plus that margin (cut edges of the oracle's
+    window are wrong by then only within the margin, which is discarded; where the window touches the real
+    ring the oracle's fixed ring IS the ring).  Windows: this rank's first rows (strip boundary, ghost rows
+    included), middle, last rows  x  first columns, a CTA-column boundary in the middle, last columns.
+    view = (lo, nloc, lo_c, nyloc): the global rows / columns this rank's local array holds;
+    get(r0, r1, c0, c1) -> numpy window of the newest local array in GLOBAL coordinates."""
+    import numpy as np
+    from oracle import pyoracle as O
+    nx, ny, U = wl["nx"], wl["ny"], updates
+    lo, nloc, lo_c, nyloc = view
+    hi, hi_c = lo + nloc, lo_c + nyloc
+    H, Wd = 40, 64
+    rows = {(lo, min(lo + H, hi)), (max(lo, (lo + hi) // 2 - H // 2), min(hi, (lo + hi) // 2 + H // 2)), (max(lo, hi - H), hi)}
+    mid_c = max(lo_c, min(hi_c - Wd, (lo_c + hi_c) // 2 // 512 * 512 - Wd // 2))
+    cols = {(lo_c, min(lo_c + Wd, hi_c)), (mid_c, min(mid_c + Wd, hi_c)), (max(lo_c, hi_c - Wd), hi_c)}
+    n_win = n_pts = n_bad = 0
+    for (r0, r1) in sorted(rows):
+        for (c0, c1) in sorted(cols):
+            R0, R1, C0, C1 = max(0, r0 - U), min(nx, r1 + U), max(0, c0 - U), min(ny, c1 + U)
+            want, _, _ = O.solve(inidat_window(nx, ny, R0, R1, C0, C1), U, arith=arith)
+            want = want[r0 - R0:r1 - R0, c0 - C0:c1 - C0]
+            got = get(r0, r1, c0, c1)
+            n_bad += int((got.view(np.uint32) != want.view(np.uint32)).sum())
+            n_win += 1
+            n_pts += got.size
+    return n_win, n_pts, n_bad
+
+
+def run_one(ctx, api, wl, arith, args):
+    """One workload on this rank's GPU: build the solver, measure, check parity.  Returns a dict."""
+    torch, dist, world = ctx.torch, ctx.dist, ctx.world
+    nx, ny = wl["nx"], wl["ny"]
+    T = wl["temporal_block"]
+    params = dict(arith=arith, conv_every=wl["conv_every"], temporal_block=T)
+    s = None
+    if world > 1:
+        from parallel_heat_b200.strips import StripSolver
+        s = StripSolver(nx, ny, device=ctx.local_rank, halo=args.halo, cols=args.cols, **params)
+        solver = s.solver
+        if args.halo == "p2p":
+            solver.set_stream(ctx.stream.cuda_stream)
+        init, enqueue, sync = s.init_inidat, s.enqueue, s.sync
+        rows_own, cols_own = s.rows, s.ncols
+        lo_c = s.col0 - 1 if (args.cols > 1 and s.by > 0) else 0
+        hi_c = s.col0 + s.ncols + 1 if (args.cols > 1 and s.by < args.cols - 1) else ny
+    else:
+        solver = api.HeatSolver(nx, ny, device=ctx.local_rank, **params)
+        solver.set_stream(ctx.stream.cuda_stream)
+        init, enqueue, sync = solver.init_inidat, solver.enqueue, solver.sync
+        rows_own, cols_own, lo_c, hi_c = nx, ny, 0, ny
+    try:
+        init()
+        K, W = args.steps, max(args.warmup, 3)
+        if T > 1:
+            K = max(K // T, 1) * T
+        if wl["conv_every"] > 0:
+            # the convergence-check loop is host-driven every conv_every updates: time heat_run itself
+            def enqueue(n):  # noqa: F811
+                solver.run(n)
+        m = measure(ctx, enqueue, sync, K, W, reps=args.reps or None, launch_count=solver.launch_count)
+        launches = m["launches"]  # this rank's kernel launches between the first and the last timed event
+        ms = m["median_ms"]
+        lups_per_update = (nx - 2) * (ny - 2)
+        value = lups_per_update * K / (ms * 1e-3) / 1e9
+
+        # roofline of the dominant kernel (the update kernel): this rank's algorithmic bytes per launch
+        peak, peak_src = measured_peak()
+        step_launches = K // T
+        own_lups = (min(rows_own, nx - 2) if world > 1 else nx - 2) * min(cols_own, ny - 2) * T
+        kernel_ms = ms / max(step_launches, 1)
+        achieved = BYTES_PER_LUP * own_lups / (kernel_ms * 1e-3) / 1e9
+        kname = "heat_step_tb" if T > 1 else "heat_step_vec"
+        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                    "traffic": ncu_traffic(f"{kname}@{wl['name']}") or ncu_traffic(kname), "kernel": kname, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": BYTES_PER_LUP * own_lups,
+                    "note": "8 B per point-update x interior points of this GPU's strip / (median repetition / launches per repetition)"
+                            + (" (effective: temporal blocking re-uses tiles on chip)" if T > 1 else "")}
+
+        # parity of this very code path (same solver object, same kernels, same neighbours), outside the timed region
+        parity = None
+        if not args.no_parity:
+            init()
+            U = PARITY_UPDATES
+            enqueue(U)  # the timed call (heat_run when there is a convergence check, else heat_enqueue)
+            sync()
+            ctx.barrier()
+            ptr, pitch, nloc, lo = solver.device_view(0)
+
+            def get(r0, r1, c0, c1):
+                return device_window(torch, ptr, pitch, r0 - lo, r1 - lo, c0 - lo_c, c1 - lo_c, ctx.local_rank)
+            nw, npts, nbad = parity_windows(ctx, wl, arith, (lo, nloc, lo_c, hi_c - lo_c), U, get)
+            if world > 1:
+                t = torch.tensor([nw, npts, nbad], device="cuda", dtype=torch.float64)
+                dist.all_reduce(t)
+                nw, npts, nbad = (int(x) for x in t.tolist())
+            parity = {"windows": nw, "points": npts, "mismatches": nbad, "bit_exact": nbad == 0, "updates": U,
+                      "against": "oracle.solve on each window + margin (40x64 windows: strip boundaries incl. ghost rows, "
+                                 "middle, field edges), after re-initialising and running the same enqueue path"}
+        out = {"value": value, "unit": "GLUP/s", "ms_per_step": ms / K, "steps": K, "reps": m["reps"],
+               "rep_ms": {"best": m["best_ms"], "median": m["median_ms"], "worst": m["worst_ms"], "mean": m["mean_ms"]},
+               "per_rank_median_ms": m["per_rank_median_ms"], "roofline": roofline, "clocks": m["clocks"],
+               "gpu_launches": int(launches), "parity": parity}
+        return out
+    finally:
+        if s is not None:
+            s.close()
+        else:
+            solver.close()
+
+
+def e2e_single(ctx, api, wl, arith, K):
+    """heat_solve() on pinned HOST memory: H2D + K updates + D2H inside the timed region, wall clock, median of 3."""
+    import ctypes as C
+    torch = ctx.torch
+    nx, ny, T = wl["nx"], wl["ny"], wl["temporal_block"]
+    params = dict(arith=arith, conv_every=wl["conv_every"], temporal_block=T)
+    host = torch.empty((nx, ny), dtype=torch.float32, pin_memory=True)
+    start = torch.empty((nx, ny), dtype=torch.float32, pin_memory=True) if nx * ny <= 16384 * 16384 else None
+    hn = host.numpy()
+    with api.HeatSolver(nx, ny, device=ctx.local_rank, arith=arith) as tmp:  # the inidat field, made on the device
+        tmp.init_inidat()
+        tmp.download(hn)
+    if start is not None:
+        start.copy_(host)
+    p = api.default_params(nx=nx, ny=ny, steps=K, device=ctx.local_rank, **params)
+    lib = api.load()
+    secs, done = [], C.c_int(0)
+    conv = C.c_int(0)
+    runs = 3
+    for k in range(runs + 1):  # the first call is a warm-up (context pools, pinned-page mappings)
+        if k > 0:
+            if start is not None:
+                host.copy_(start)
+            else:  # 65536^2: re-create the field in place instead of keeping a second 16 GiB pinned copy
+                with api.HeatSolver(nx, ny, device=ctx.local_rank, arith=arith) as tmp:
+                    tmp.init_inidat()
+                    tmp.download(hn)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        rc = lib.heat_solve(C.byref(p), hn.ctypes.data_as(C.POINTER(C.c_float)), C.byref(done), C.byref(conv))
+        dt = time.perf_counter() - t0
+        if rc != 0:
+            raise RuntimeError(lib.heat_last_error().decode())
+        if k > 0:
+            secs.append(dt)
+    dt = sorted(secs)[len(secs) // 2]
+    # the host result of the last call, checked like the device result
+    import numpy as np
+    from oracle import pyoracle as O  # noqa: F401
+    nw, npts, nbad = parity_windows(ctx, wl, arith, (0, nx, 0, ny), done.value, lambda r0, r1, c0, c1: np.ascontiguousarray(hn[r0:r1, c0:c1]))
+    lups = (nx - 2) * (ny - 2)
+    return {"value": lups * done.value / dt / 1e9, "unit": "GLUP/s",
+            "h2d_bytes_per_step": nx * ny * 4 / max(done.value, 1), "d2h_bytes_per_step": nx * ny * 4 / max(done.value, 1),
+            "call": f"heat_solve(steps={K}) on pinned host memory: cudaMalloc + H2D of the {nx * ny * 4 >> 20} MiB field "
+                    f"+ {done.value} updates + D2H (the three overlap band by band), wall clock, median of {runs} calls after one warm-up call",
+            "seconds": dt, "seconds_all": secs, "pcie_gbs_each_way": nx * ny * 4 / dt / 1e9,
+            "parity": {"windows": nw, "points": npts, "mismatches": nbad, "bit_exact": nbad == 0, "updates": done.value}}
+
+
+def e2e_strips(ctx, api, wl, arith, args):
+    """Strips: every rank brings its own window of the field in pinned host memory, uploads it, runs K updates and
+    reads its rows back; wall clock between barriers (max over ranks by construction)."""
+    torch, dist = ctx.torch, ctx.dist
+    from parallel_heat_b200.strips import StripSolver
+    nx, ny, T = wl["nx"], wl["ny"], wl["temporal_block"]
+    K = max(args.steps // T, 1) * T
+    s = StripSolver(nx, ny, device=ctx.local_rank, halo=args.halo, cols=1, arith=arith, conv_every=0, temporal_block=T)
+    try:
+        solver = s.solver
+        if args.halo == "p2p":
+            solver.set_stream(ctx.stream.cuda_stream)
+        s.init_inidat()
+        _, _, nloc, lo = solver.device_view(0)
+        host = torch.empty((nloc, ny), dtype=torch.float32, pin_memory=True)
+        host.numpy()[...] = inidat_window(nx, ny, lo, lo + nloc, 0, ny)
+        back = torch.empty((s.rows, ny), dtype=torch.float32, pin_memory=True)
+        secs = []
+        for k in range(3):  # first round = warm-up
+            ctx.barrier()
+            t0 = time.perf_counter()
+            solver.upload_local(host.numpy())
+            dist.barrier()  # nobody stores into a neighbour whose upload has not landed (flags order it; belt and braces)
+            s.enqueue(K)
+            s.sync()
+            solver.download_local(back.numpy())
+            ctx.barrier()
+            if k > 0:
+                secs.append(time.perf_counter() - t0)
+        dt = sorted(secs)[len(secs) // 2]
+        tot = torch.tensor([float(nloc * ny * 4), float(s.rows * ny * 4), dt], device="cuda", dtype=torch.float64)
+        mx = tot.clone()
+        dist.all_reduce(tot)
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dt = float(mx[2].item())
+        return {"value": (nx - 2) * (ny - 2) * K / dt / 1e9, "unit": "GLUP/s",
+                "h2d_bytes_per_step": float(tot[0].item()) / K, "d2h_bytes_per_step": float(tot[1].item()) / K,
+                "call": f"per rank: heat_upload_local (pinned host window) + {K} updates + heat_download_local, "
+                        "wall clock between barriers, median of 2 rounds after one warm-up round, max over ranks", "seconds": dt}
+    finally:
+        s.close()
+
+
+def run_ours(args, wl, rank, world, local_rank):
     import torch
     import torch.distributed as dist
 
@@ -255,206 +611,101 @@ def run_ours(args, wl, rank, world, local_rank):
         dist.barrier()
     api.load()
     torch.cuda.set_device(local_rank)
-    nx, ny = wl["nx"], wl["ny"]
     arith = {"fma": api.F32_FMA, "nofma": api.F32_NOFMA, "f64mix": api.MPI_F64MIX}[args.arith]
-    params = dict(arith=arith, conv_every=wl["conv_every"], temporal_block=wl["temporal_block"])
     stream = torch.cuda.current_stream()
+    clocks = ClockSampler(local_rank).start()  # NVML initialised here, long before any timed region
+    ctx = Ctx(torch, dist, rank, world, local_rank, stream, clocks)
+    peak, _ = measured_peak()
+    try:
+        main = run_one(ctx, api, wl, arith, args)
 
-    if world > 1:
-        from parallel_heat_b200.strips import StripSolver
-        s = StripSolver(nx, ny, device=local_rank, halo=args.halo, cols=args.cols, **params)
-        solver = s.solver
-        if args.halo == "p2p":
-            solver.set_stream(stream.cuda_stream)
-        s.init_inidat()
-        enqueue, sync = s.enqueue, s.sync
-        rows_own = s.rows
-        cols_own = s.ncols
-    else:
-        solver = api.HeatSolver(nx, ny, device=local_rank, **params)
-        solver.set_stream(stream.cuda_stream)
-        solver.init_inidat()
-        enqueue, sync = solver.enqueue, solver.sync
-        rows_own = nx
-        cols_own = ny
+        e2e = None
+        if not args.no_e2e:
+            if world == 1:
+                e2e = e2e_single(ctx, api, wl, arith, max(args.steps // wl["temporal_block"], 1) * wl["temporal_block"])
+            elif args.cols == 1:
+                e2e = e2e_strips(ctx, api, wl, arith, args)
 
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-            torch.cuda.synchronize()
+        # the other 1-GPU configurations of BASELINE.json, measured the same way, reported next to the headline
+        also = None
+        if world == 1 and not args.no_also:
+            also = {}
 
-    K, W = args.steps, max(args.warmup, 3)
-    if wl["conv_every"] > 0:
-        # the convergence-check loop is host-driven every conv_every updates: time heat_run itself
-        def enqueue(n):  # noqa: F811
-            solver.run(n)
-    enqueue(W)
-    sync()
-    barrier()
-    launches0 = solver.launch_count()
-    clocks = ClockSampler(local_rank)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    clocks.start()
-    e0.record(stream)
-    enqueue(K)
-    e1.record(stream)
-    sync()
-    barrier()
-    clk = clocks.stop()
-    ms = e0.elapsed_time(e1)
-    launches = solver.launch_count() - launches0
-    if world > 1:
-        t = torch.tensor([ms], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    lups_per_update = (nx - 2) * (ny - 2)
-    value = lups_per_update * K / (ms * 1e-3) / 1e9
+            def leg(key, name, arith_, note, tb=None):
+                w = workload(name, 1)
+                if tb:
+                    w["temporal_block"] = tb
+                r = run_one(ctx, api, w, arith_, args)
+                r["workload"] = w["text"] + (f", {tb} updates per HBM pass" if tb else "")
+                r["arith"] = api.ARITH_NAMES[arith_]
+                r["note"] = note
+                if w["temporal_block"] > 1:
+                    r["effective_gbs"] = r["value"] * BYTES_PER_LUP
+                    r["effective_frac"] = r["value"] * BYTES_PER_LUP / peak
+                also[key] = r
 
-    # roofline of the dominant kernel (the update kernel): this rank's algorithmic bytes per launch
-    peak, peak_src = measured_peak()
-    step_launches = K // wl["temporal_block"] if wl["temporal_block"] > 1 else K
-    own_lups = (min(rows_own, nx - 2) if world > 1 else nx - 2) * min(cols_own, ny - 2) * wl["temporal_block"]
-    kernel_ms = ms / max(step_launches, 1)
-    achieved = BYTES_PER_LUP * own_lups / (kernel_ms * 1e-3) / 1e9
-    kname = "heat_step_tb" if wl["temporal_block"] > 1 else "heat_step_vec"
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": ncu_traffic(kname), "kernel": kname, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": BYTES_PER_LUP * own_lups,
-                "note": "8 B per point-update x interior points of this GPU's strip / mean launch time over the timed region"
-                        + (" (effective: temporal blocking re-uses tiles on chip)" if wl["temporal_block"] > 1 else "")}
+            if wl["name"] != "c3":
+                leg("c3_16384", "c3", arith, "BASELINE configs[2]: convergence check every 20 updates fused into the update "
+                    "kernel (K2), one 4-byte read-back per check; north_star's >= 80 % target is quoted on this grid")
+            if wl["name"] != "c2":
+                leg("c2_8192", "c2", arith, "BASELINE configs[1]: 8192x8192, no convergence check")
+            if wl["name"] != "weak32k":
+                leg("weak32k_T4", "weak32k", arith, "BASELINE configs[4] at 1 GPU: heat_step_tb<T=4>, 4 updates per pass, same bits "
+                    "as 4 single updates; 8 B/LUP counted as for single-step, so frac is EFFECTIVE bandwidth")
+            if wl["temporal_block"] == 1 and wl["conv_every"] == 0:
+                leg(wl["name"] + "_T4", wl["name"], arith, "the headline workload with 4 updates fused per HBM pass (bit-identical)", tb=4)
+            if arith != api.MPI_F64MIX:
+                leg("mpi_f64mix", wl["name"], api.MPI_F64MIX, "the headline workload in the MPI program's mixed float/double "
+                    "arithmetic (M:168-174): bit-identical to what the --impl reference arm computes")
+                if wl["name"] != "c2":
+                    leg("mpi_f64mix_c2_8192", "c2", api.MPI_F64MIX, "8192x8192 in the MPI program's arithmetic")
+            also["reference_cuda"] = reference_cuda_leg(peak)
 
-    # end to end: heat_solve() on HOST memory (pinned), H2D + K updates + D2H inside the timed region
-    e2e = None
-    if world == 1 and not args.no_e2e:
-        host = torch.empty((nx, ny), dtype=torch.float32, pin_memory=True)
-        hn = host.numpy()
-        hn[...] = api.inidat(nx, ny)
-        p = api.default_params(nx=nx, ny=ny, steps=K, device=local_rank, **params)
-        import ctypes as C
-        done, conv = C.c_int(0), C.c_int(0)
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        rc = api.load().heat_solve(C.byref(p), hn.ctypes.data_as(C.POINTER(C.c_float)), C.byref(done), C.byref(conv))
-        dt = time.perf_counter() - t0
-        if rc != 0:
-            raise RuntimeError(api.load().heat_last_error().decode())
-        e2e = {"value": lups_per_update * done.value / dt / 1e9, "unit": "GLUP/s",
-               "h2d_bytes_per_step": nx * ny * 4 / max(done.value, 1), "d2h_bytes_per_step": nx * ny * 4 / max(done.value, 1),
-               "call": f"heat_solve(steps={K}) on pinned host memory: cudaMalloc + H2D of the {nx * ny * 4 >> 20} MiB field "
-                       f"+ {done.value} updates + D2H, wall clock", "seconds": dt}
-        launches_e2e = done.value
-    elif world > 1 and not args.no_e2e and args.cols == 1:
-        # strips: every rank brings its own window of the field in pinned host memory, uploads it,
-        # runs K updates and reads its rows back; wall clock between barriers (max over ranks)
-        _, _, nloc, lo = solver.device_view(0)
-        host = torch.empty((nloc, ny), dtype=torch.float32, pin_memory=True)
-        ix = np.arange(lo, lo + nloc, dtype=np.uint32)[:, None]
-        iy = np.arange(ny, dtype=np.uint32)[None, :]
-        prod = ix * (np.uint32(nx) - ix - np.uint32(1)) * iy * (np.uint32(ny) - iy - np.uint32(1))  # M:320, wraps like int
-        host.numpy()[...] = prod.view(np.int32).astype(np.float32)
-        back = torch.empty((rows_own, ny), dtype=torch.float32, pin_memory=True)
-        barrier()
-        t0 = time.perf_counter()
-        solver.upload_local(host.numpy())
-        dist.barrier()  # nobody stores into a neighbour whose upload has not landed (flags order it; this is belt and braces)
-        enqueue(K)
-        sync()
-        solver.download_local(back.numpy())
-        barrier()
-        dt = time.perf_counter() - t0
-        tot_in = torch.tensor([float(nloc * ny * 4)], device="cuda")
-        tot_out = torch.tensor([float(rows_own * ny * 4)], device="cuda")
-        dist.all_reduce(tot_in)
-        dist.all_reduce(tot_out)
-        e2e = {"value": lups_per_update * K / dt / 1e9, "unit": "GLUP/s",
-               "h2d_bytes_per_step": float(tot_in.item()) / K, "d2h_bytes_per_step": float(tot_out.item()) / K,
-               "call": f"per rank: heat_upload_local (pinned host window) + {K} updates + heat_download_local, "
-                       "wall clock between barriers", "seconds": dt}
-
-    # the same job with 4 updates fused per pass over HBM (bit-identical result): reported next to the
-    # single-step number, never instead of it
-    also = None
-    if world == 1 and wl["temporal_block"] == 1 and wl["conv_every"] == 0 and not args.no_also:
-        with api.HeatSolver(nx, ny, device=local_rank, arith=arith, temporal_block=4) as s4:
-            s4.set_stream(stream.cuda_stream)
-            s4.init_inidat()
-            s4.enqueue(4 * max(W // 4, 1))
-            s4.sync()
-            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            k4 = max(K // 4, 1) * 4
-            a0.record(stream)
-            s4.enqueue(k4)
-            a1.record(stream)
-            s4.sync()
-            ms4 = a0.elapsed_time(a1)
-        v4 = lups_per_update * k4 / (ms4 * 1e-3) / 1e9
-        also = {"temporal_block_4": {"value": v4, "unit": "GLUP/s", "ms_per_step": ms4 / k4, "steps": k4,
-                                     "effective_gbs": v4 * BYTES_PER_LUP, "effective_frac": v4 * BYTES_PER_LUP / peak,
-                                     "traffic": ncu_traffic("heat_step_tb"),
-                                     "note": "heat_step_tb<T=4>: 4 updates per pass, same bits as 4 single updates; "
-                                             "8 B/LUP counted as for single-step, so this is EFFECTIVE bandwidth"}}
-
-        # and in the arithmetic of the MPI reference (bit-identical to the program --impl reference times)
-        if arith != api.MPI_F64MIX:
-            with api.HeatSolver(nx, ny, device=local_rank, arith=api.MPI_F64MIX) as s6:
-                s6.set_stream(stream.cuda_stream)
-                s6.init_inidat()
-                s6.enqueue(W)
-                s6.sync()
-                k6 = max(K // 4, 16)
-                a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                a0.record(stream)
-                s6.enqueue(k6)
-                a1.record(stream)
-                s6.sync()
-                ms6 = a0.elapsed_time(a1)
-            v6 = lups_per_update * k6 / (ms6 * 1e-3) / 1e9
-            also["mpi_f64mix"] = {"value": v6, "unit": "GLUP/s", "ms_per_step": ms6 / k6, "steps": k6,
-                                  "frac": v6 * BYTES_PER_LUP / peak,
-                                  "note": "same kernel in the MPI program's mixed float/double arithmetic (M:168-174), "
-                                          "bit-identical to the reference arm's output; FP64-pipe-bound"}
-
-    base = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        base = cpu_baseline(wl)
+        base = None
+        if rank == 0 and world == 1 and not args.no_cpu_baseline:
+            base = cpu_baseline(wl)
+    finally:
+        clocks.stop()
 
     if rank == 0:
-        out = {"metric": METRIC, "value": value, "unit": "GLUP/s", "n_gpus": world, "steps": K, "warmup": W,
-               "ms_per_step": ms / K, "higher_is_better": True, "scaling": wl["scaling"], "vs_baseline": None,
-               "dtype": "f32" if arith != api.MPI_F64MIX else "f32 grid, f64-mixed arithmetic",
-               "data": "synthetic",
-               "config": {"workload": wl["text"], "nx": nx, "ny": ny, "arith": api.ARITH_NAMES[arith],
-                          "arith_note": "F32_FMA = bit-identical to the reference cuda_heat.cu (nvcc default); the MPI reference "
-                                        "computes in MPI_F64MIX (see also.mpi_f64mix); the two differ by < 1e-5 relative",
-                          "conv_every": wl["conv_every"], "temporal_block": wl["temporal_block"],
-                          "halo": (args.halo if world > 1 else "none"),
-                          "decomposition": (f"{world // args.cols}x{args.cols} blocks" if world > 1 else "single"),
-                          "l2": f"working set {2 * nx * ny * 4 >> 20} MiB vs 126 MB L2: inputs larger than L2, no flush "
-                                "(consecutive updates ARE the workload)"},
-               "roofline": roofline, "cpu_baseline": base, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
-               "also": also}
+        cfg = config_of(wl, api.ARITH_NAMES[arith], world, args.halo, args.cols)
+        cfg["arith_note"] = ("F32_FMA = bit-identical to the reference cuda_heat.cu (nvcc default); the MPI reference computes in "
+                             "MPI_F64MIX (see also.mpi_f64mix); the two differ by < 1e-5 relative")
+        cfg["timing"] = (f"{main['reps']} repetitions of {main['steps']} updates back to back, each between its own CUDA events; per "
+                         "repetition max over ranks; ms_per_step = median repetition / steps; warm-up = W updates + one untimed "
+                         f"repetition + {LOCKSTEP_UPDATES} lockstep updates after the barrier")
+        out = {"metric": METRIC, "value": main["value"], "unit": "GLUP/s", "n_gpus": world, "steps": main["steps"],
+               "warmup": max(args.warmup, 3), "ms_per_step": main["ms_per_step"], "higher_is_better": True,
+               "scaling": wl["scaling"], "vs_baseline": None,
+               "dtype": "f32" if arith != api.MPI_F64MIX else "f32 grid, f64-mixed arithmetic", "data": "synthetic",
+               "config": cfg, "reps": main["reps"], "rep_ms": main["rep_ms"], "per_rank_median_ms": main["per_rank_median_ms"],
+               "roofline": main["roofline"], "cpu_baseline": base, "e2e": e2e, "gpu_launches": main["gpu_launches"],
+               "clocks": main["clocks"], "parity": main["parity"], "also": also}
         print(json.dumps(out), flush=True)
-    if world > 1:
-        s.close()
-    else:
-        solver.close()
+    bad = main["parity"] is not None and not main["parity"]["bit_exact"]
+    if e2e and e2e.get("parity") and not e2e["parity"]["bit_exact"]:
+        bad = True
+    if also:
+        bad = bad or any(isinstance(v, dict) and v.get("parity") and not v["parity"]["bit_exact"] for v in also.values())
+    return 3 if bad else 0
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10000)
-    ap.add_argument("--warmup", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--reps", type=int, default=0, help="timed repetitions (default: >= 7, enough for a 250 ms region)")
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
-    ap.add_argument("--workload", default="c2")
+    ap.add_argument("--workload", default="strong")
     ap.add_argument("--arith", choices=["fma", "nofma", "f64mix"], default="fma")
     ap.add_argument("--halo", choices=["p2p", "sendrecv"], default="p2p")
     ap.add_argument("--cols", type=int, default=1, help="N>1: 2-D blocks with this many column blocks (default: row strips)")
     ap.add_argument("--temporal-block", type=int, default=0, help="override the workload's updates per HBM pass (1, 2, 4)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-also", action="store_true", help="skip the extra temporal-block-4 measurement")
+    ap.add_argument("--no-also", action="store_true", help="skip the other 1-GPU configurations")
+    ap.add_argument("--no-parity", action="store_true", help="skip the bit-exact window check after the timed region")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -475,12 +726,11 @@ def main():
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:
-        run_ours(args, wl, rank, world, local_rank)
+        return run_ours(args, wl, rank, world, local_rank)
     finally:
         if world > 1:
             import torch.distributed as dist
             dist.destroy_process_group()
-    return 0
 
 
 if __name__ == "__main__":

@@ -91,7 +91,12 @@ int heat_readdat_bin(const char *fnam, int *nx, int *ny, float *u, size_t capaci
 /* ---- one-shot: the whole loop region with caller-owned HOST memory -------------------
  * Replaces C:176-242 (cudaMalloc, H2D to both buffers, step loop, D2H) and, on one strip,
  * M:129-269.  grid: in = initial field, out = newest field.  updates_done = Jacobi updates
- * executed; the reference programs print updates_done-1 when they converge (M:302, C:256). */
+ * executed; the reference programs print updates_done-1 when they converge (M:302, C:256).
+ * Without a convergence check, and when steps is small against nx, the three phases overlap: the field
+ * streams through the GPU in bands of rows (H2D of band i+1, all updates of band i -- time-skewed -- and
+ * D2H of the rows that are final run at the same time; same bits as the plain loop).  Pass page-locked
+ * memory (cudaHostAlloc / cudaHostRegister) to get that overlap; pageable memory works but copies
+ * synchronously.  HEAT_SOLVE_STREAMED=0 switches the overlap off, HEAT_SOLVE_BAND_ROWS sets the band. */
 int heat_solve(const heat_params *p, float *grid, int *updates_done, int *converged);
 
 /* The same over the first `ngpus` devices of this process: one row strip per GPU, ghost rows moved by
@@ -100,12 +105,20 @@ int heat_solve(const heat_params *p, float *grid, int *updates_done, int *conver
 int heat_solve_gpus(const heat_params *p, int ngpus, float *grid, int *updates_done, int *converged);
 
 /* ---- device-resident handle (what C keeps alive in dvc_grids[2], C:177-198) ---------- */
+/* The field of a new handle is unspecified until heat_upload* / heat_init_inidat (a handle that is
+ * run without either starts from a zero field).  Everything the time loop needs -- CUDA graphs of 16
+ * passes, occupancy queries, scratch of the resident-field kernel -- is built when the field arrives,
+ * not by the first heat_enqueue / heat_run. */
 int heat_create(const heat_params *p, heat_handle **out);
 int heat_destroy(heat_handle *h);
 /* Use the caller's CUDA stream (a cudaStream_t passed as void*) instead of the handle's own. */
 int heat_set_stream(heat_handle *h, void *cuda_stream);
 /* Host -> device of the FULL nx*ny field into BOTH buffers (C:197-198); a strip takes its rows
- * (ghost rows included), a 2-D block its rows x columns window (ghost columns included). */
+ * (ghost rows included), a 2-D block its rows x columns window (ghost columns included).
+ * Strips connected across processes: every strip of the job must upload the same number of times
+ * (an upload is one epoch of the step flags); before the copy the call waits on the device until the
+ * neighbours have finished the pass this strip finished last, so that none of their ghost-row stores
+ * can land on top of the new field. */
 int heat_upload(heat_handle *h, const float *full_grid);
 /* Same from a device pointer holding the full field (used when the field is already in HBM). */
 int heat_upload_device(heat_handle *h, const void *d_full_grid);
@@ -161,7 +174,14 @@ int heat_step_residual_device(const void *d_in, void *d_out, int nx, int ny, flo
  * max|old-new|; nothing needs zeroing beforehand.  Limits and rules: ny <= HEAT_NOALLOC_MAX_NY,
  * larger rows are refused with HEAT_E_INVALID; all calls on one GPU share the array, so calls
  * that overlap on that GPU race -- issue them one after another; the first call on a GPU
- * looks up the array's address and should be made outside any stream capture. */
+ * looks up the array's address and should be made outside any stream capture.
+ * The array that is used is the one of the device that is CURRENT in the calling thread: make the
+ * device that owns d_in, d_out, d_residual and the stream current (cudaSetDevice) before the
+ * call, as you would for a kernel launch of your own.  Two limits of the "no allocation" promise:
+ * with CUDA's lazy module loading the FIRST call on a GPU makes the driver load the library's
+ * code and this array onto that GPU, which takes device memory once -- every later call allocates
+ * nothing; and the address found by that first call is kept for the life of the process, so it
+ * does not survive cudaDeviceReset() -- do not reset a device between calls. */
 #define HEAT_NOALLOC_MAX_BLOCKS    16384
 #define HEAT_NOALLOC_SCRATCH_BYTES ((HEAT_NOALLOC_MAX_BLOCKS + 64) * 4)
 #define HEAT_NOALLOC_MAX_NY        (HEAT_NOALLOC_MAX_BLOCKS * 256 + 2)

@@ -93,6 +93,9 @@ DEFAULT_MPI = [
     (1024, 1024, True, True, "O3"),
     (8192, 8192, False, True, "O3"), (8192, 8192, False, True, "O0"),
     (16384, 16384, True, True, "O3"),
+    # bench.py's reference arm for the 65536^2 / 32768^2 workloads: the largest grid whose whole program
+    # (inidat, two prtdat walks, 5 field copies) ends inside the time-box
+    (16384, 16384, False, True, "O3"),
     # bench.py --impl reference at N GPUs: the weak-scaling grid (8192*N) x 8192
     (16384, 8192, False, True, "O3"), (32768, 8192, False, True, "O3"), (65536, 8192, False, True, "O3"),
 ]

@@ -225,7 +225,9 @@ struct heat_handle {
     int64_t launches = 0;
     int rows_per_tile = 0;
     int rows_per_tile_tb = 0;     // 0 = choose per launch
+    int tb_per_sm = 0;            // resident CTAs per SM of this handle's K4 instantiation (queried once)
     int sm_count = 148;
+    bool loaded = false;          // a field has been uploaded / initialised (else the first use zero-fills)
     // neighbours: side 0 = north (lower rows), 1 = south, 2 = west (lower columns), 3 = east
     unsigned* d_edge_count = nullptr;    // [4] edge-CTA arrival counters of the fused strip ordering, per side
     strip_sync sync_args = {};           // filled per pass for flag-ordered strips, else all null
@@ -381,8 +383,12 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     CKH(cudaHostGetDevicePointer((void**)&h->d_status, h->h_status, 0));
     CKH(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     h->own_stream = true;
-    CKH(cudaMemsetAsync(h->buf[0], 0, bytes, h->stream));
-    CKH(cudaMemsetAsync(h->buf[1], 0, bytes, h->stream));
+    // heat_upload / heat_init_inidat overwrite every row and column of the field; only the padding columns
+    // [nyloc, pitch), which the kernels load and copy through, must hold something harmless
+    if (h->pitch > h->nyloc)
+        for (int k = 0; k < 2; k++)
+            CKH(cudaMemset2DAsync(h->buf[k] + h->nyloc, h->pitch * sizeof(float), 0, (size_t)(h->pitch - h->nyloc) * sizeof(float),
+                                  h->nloc, h->stream));
     CKH(cudaMemsetAsync(h->flags, 0, 4 * sizeof(unsigned long long), h->stream));
     CKH(cudaMemsetAsync(h->d_resid, 0, sizeof(unsigned), h->stream));
     CKH(cudaMemsetAsync(h->d_edge_count, 0, 4 * sizeof(unsigned), h->stream));
@@ -505,15 +511,15 @@ static cudaError_t launch_tb_t(heat_handle* h, const float* in, float* out, floa
         // best R = 48 / 96 / 128-192 / 128-256 rows at 8192^2 / 16384^2 / 32768^2 / 65536^2, i.e. the
         // band of all resident CTAs is about 2400 rows tall whatever the row length.  Modelling the
         // CTAs as rounds of `resident` (R = 168 at 8192^2: one exact round) was 12 % slower.
-        static int per_sm_cached = 0; // same for every handle of this instantiation
-        if (per_sm_cached < 1 &&
-            (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_cached, heat_step_tb<ARITH, T, WARPS, false>, WARPS * 32, 0) !=
+        // resident CTAs per SM of this instantiation on this handle's device: queried once per handle
+        if (h->tb_per_sm < 1 &&
+            (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->tb_per_sm, heat_step_tb<ARITH, T, WARPS, false>, WARPS * 32, 0) !=
                  cudaSuccess ||
-             per_sm_cached < 1)) {
+             h->tb_per_sm < 1)) {
             cudaGetLastError();
-            per_sm_cached = 6;
+            h->tb_per_sm = 6;
         }
-        const int per_sm = per_sm_cached;
+        const int per_sm = h->tb_per_sm;
         const long long resident = (long long)per_sm * h->sm_count, colblocks = (wcols + WARPS - 1) / WARPS;
         // (multiples of 3: the kernel's row loop is unrolled by 3)
         rpt = (int)((2400 * colblocks / resident + 12) / 24 * 24);
@@ -740,34 +746,73 @@ static int launch_resident(heat_handle* h, int updates)
 // one launch per update, 2-4 us each in the reference's own Table 6.
 static const int GRAPH_PASSES = 16;
 
+// Captures GRAPH_PASSES passes starting from (newest buffer `cur`, sweep direction `dir`) and instantiates them.
+static int build_pass_graph(heat_handle* h, int cur, int dir, int fused, cudaGraphExec_t* exec)
+{
+    if (!h->capture_stream) CK(cudaStreamCreateWithFlags(&h->capture_stream, cudaStreamNonBlocking));
+    const cudaStream_t user = h->stream;
+    const long long it0 = h->it, sweeps0 = h->sweeps;
+    const int cur0 = h->cur;
+    const unsigned long long seq0 = h->seq;
+    const int64_t launches0 = h->launches;
+    cudaGraph_t graph = nullptr;
+    h->stream = h->capture_stream;
+    h->cur = cur;
+    h->sweeps = dir;
+    cudaError_t e = cudaStreamBeginCapture(h->capture_stream, cudaStreamCaptureModeRelaxed);
+    int rc = HEAT_OK;
+    if (e == cudaSuccess) {
+        for (int k = 0; k < GRAPH_PASSES && !rc; k++) rc = enqueue_update(h, false, fused);
+        e = cudaStreamEndCapture(h->capture_stream, &graph);
+    }
+    h->stream = user;
+    h->it = it0, h->sweeps = sweeps0, h->seq = seq0, h->launches = launches0, h->cur = cur0; // nothing ran yet
+    if (rc) {
+        if (graph) cudaGraphDestroy(graph);
+        return rc;
+    }
+    if (e != cudaSuccess || !graph) return fail(HEAT_E_CUDA, "stream capture failed: %s", cudaGetErrorString(e));
+    e = cudaGraphInstantiate(exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) return fail(HEAT_E_CUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(e));
+    // the first launch of an executable graph uploads it to the device: do that now, not in the caller's loop
+    e = cudaGraphUpload(*exec, user);
+    if (e != cudaSuccess) cudaGetLastError(); // an optimisation only
+    return HEAT_OK;
+}
+
+static bool graphs_apply(const heat_handle* h) { return h->p.nranks == 1 && h->p.nranks_y == 1 && h->use_graphs; }
+
+// Everything a first heat_enqueue / heat_run would otherwise set up lazily, done when the field arrives
+// (heat_upload*, heat_init_inidat): the pass graphs for both buffer parities and both sweep directions, the K4
+// occupancy query, and the resident-field kernel's scratch.  A caller that times its first loop times the
+// loop, not cudaStreamBeginCapture + cudaGraphInstantiate (round 1's bench did: 0.64 ms inside a 2 ms region).
+static int prepare(heat_handle* h)
+{
+    if (h->p.nranks == 1 && h->p.nranks_y == 1 && h->use_resident) {
+        int rc = resident_prepare(h);
+        if (rc < 0) return rc;
+    }
+    // (a field that runs resident in shared memory never replays the pass graphs)
+    if (!graphs_apply(h) || h->res_ctas > 0 || h->upd_hi - h->upd_lo < 1 || h->nyloc < 3) return HEAT_OK;
+    const int fused = h->p.temporal_block;
+    for (int cur = 0; cur < 2; cur++)
+        for (int dir = 0; dir < (h->serpentine ? 2 : 1); dir++) {
+            cudaGraphExec_t& exec = h->graphs[cur][dir][fused > 1 ? 1 : 0];
+            if (exec) continue;
+            int rc = build_pass_graph(h, cur, dir, fused, &exec);
+            if (rc) return rc;
+        }
+    return HEAT_OK;
+}
+
 static int launch_pass_graph(heat_handle* h, int fused)
 {
-    cudaGraphExec_t& exec = h->graphs[h->cur][h->serpentine ? (int)(h->sweeps & 1) : 0][fused > 1 ? 1 : 0];
-    if (!exec) {
-        if (!h->capture_stream) CK(cudaStreamCreateWithFlags(&h->capture_stream, cudaStreamNonBlocking));
-        const cudaStream_t user = h->stream;
-        const long long it0 = h->it, sweeps0 = h->sweeps;
-        const int cur0 = h->cur;
-        const unsigned long long seq0 = h->seq;
-        const int64_t launches0 = h->launches;
-        cudaGraph_t graph = nullptr;
-        h->stream = h->capture_stream;
-        cudaError_t e = cudaStreamBeginCapture(h->capture_stream, cudaStreamCaptureModeRelaxed);
-        int rc = HEAT_OK;
-        if (e == cudaSuccess) {
-            for (int k = 0; k < GRAPH_PASSES && !rc; k++) rc = enqueue_update(h, false, fused);
-            e = cudaStreamEndCapture(h->capture_stream, &graph);
-        }
-        h->stream = user;
-        h->it = it0, h->sweeps = sweeps0, h->seq = seq0, h->launches = launches0, h->cur = cur0; // nothing ran yet
-        if (rc) {
-            if (graph) cudaGraphDestroy(graph);
-            return rc;
-        }
-        if (e != cudaSuccess || !graph) return fail(HEAT_E_CUDA, "stream capture failed: %s", cudaGetErrorString(e));
-        e = cudaGraphInstantiate(&exec, graph, 0);
-        cudaGraphDestroy(graph);
-        if (e != cudaSuccess) return fail(HEAT_E_CUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(e));
+    const int dir = h->serpentine ? (int)(h->sweeps & 1) : 0;
+    cudaGraphExec_t& exec = h->graphs[h->cur][dir][fused > 1 ? 1 : 0];
+    if (!exec) { // only reached when prepare() was skipped (a handle used without an upload)
+        int rc = build_pass_graph(h, h->cur, dir, fused, &exec);
+        if (rc) return rc;
     }
     CK(cudaGraphLaunch(exec, h->stream));
     h->it += (long long)GRAPH_PASSES * fused;
@@ -777,9 +822,26 @@ static int launch_pass_graph(heat_handle* h, int fused)
     return HEAT_OK;
 }
 
+// A handle that is used before any field arrived starts from a zero field (heat_create does not pay for that).
+static int ensure_loaded(heat_handle* h)
+{
+    if (h->loaded) return HEAT_OK;
+    CK(cudaSetDevice(h->p.device));
+    const size_t bytes = (size_t)h->nloc * h->pitch * sizeof(float);
+    CK(cudaMemsetAsync(h->buf[0], 0, bytes, h->stream));
+    CK(cudaMemsetAsync(h->buf[1], 0, bytes, h->stream));
+    h->loaded = true;
+    return HEAT_OK;
+}
+
 extern "C" int heat_group_enqueue(heat_handle** hs, int n, int updates)
 {
     if (!hs || n < 1 || updates < 0) return fail(HEAT_E_INVALID, "heat_group_enqueue: bad arguments");
+    for (int k = 0; k < n; k++) {
+        if (!hs[k]) return fail(HEAT_E_INVALID, "heat_group_enqueue: null handle");
+        int rc = ensure_loaded(hs[k]);
+        if (rc) return rc;
+    }
     // pass by pass across the strips: the event ordering between local strips relies on it
     const int T = hs[0]->p.temporal_block;
     for (int i = 0; i < updates;) {
@@ -846,6 +908,10 @@ extern "C" int heat_group_run(heat_handle** hs, int n, int steps, int* updates_d
     if (!hs || n < 1 || steps < 0) return fail(HEAT_E_INVALID, "heat_run: bad arguments");
     for (int k = 0; k < n; k++)
         if (!hs[k]) return fail(HEAT_E_INVALID, "heat_run: null handle");
+    for (int k = 0; k < n; k++) {
+        int rc = ensure_loaded(hs[k]);
+        if (rc) return rc;
+    }
     heat_handle* h0 = hs[0];
     const long long total = (long long)steps + (h0->p.step_convention == HEAT_STEPS_MPI ? 1 : 0);
     const int K = h0->p.conv_every;
@@ -961,10 +1027,33 @@ extern "C" int heat_set_halo_mode(heat_handle* h, int mode)
     return HEAT_OK;
 }
 
+// Flag-ordered strips (one process per GPU): a neighbour's last pass may still be storing into this strip's
+// ghost rows when heat_sync() returns here -- a pass waits only for the neighbours' PREVIOUS pass.  Before new
+// data is written over the field, wait on the device until every neighbour has finished the pass this strip
+// finished last, so that no stale ghost-row store can land on top of the upload.
+static bool has_side(const heat_handle* h, int side);
+static int quiesce_neighbours(heat_handle* h)
+{
+    if (!h->connected || h->external_halo || h->seq == 0) return HEAT_OK;
+    if (h->local_nb[0] || h->local_nb[1] || h->local_nb[2] || h->local_nb[3]) return HEAT_OK; // events order those
+    bool any = false;
+    const unsigned long long* f[4];
+    for (int side = 0; side < 4; side++) {
+        f[side] = has_side(h, side) ? &h->flags[side] : nullptr;
+        any = any || f[side];
+    }
+    if (!any) return HEAT_OK;
+    heat_wait<<<1, 32, 0, h->stream>>>(f[0], f[1], f[2], f[3], h->seq, WAIT_TIMEOUT_NS, h->d_status);
+    h->launches++;
+    CK(cudaGetLastError());
+    return HEAT_OK;
+}
+
 static int after_upload(heat_handle* h)
 {
     h->cur = 0;
     h->it = 0;
+    h->loaded = true;
     // an upload counts as one epoch of the strip flags: neighbours may not store into this
     // strip's ghost rows before the upload has landed
     h->seq++;
@@ -979,17 +1068,22 @@ static int after_upload(heat_handle* h)
             CK(cudaGetLastError());
         }
     }
+    int rc = prepare(h);
+    if (rc) return rc;
     CK(cudaStreamSynchronize(h->stream));
     return HEAT_OK;
 }
 
-static int upload_from(heat_handle* h, const void* src, cudaMemcpyKind kind)
+// src_first_row: the global row that src's first row holds (0 for a full field, h->lo for a strip's own window)
+static int upload_from(heat_handle* h, const void* src, int src_first_row, cudaMemcpyKind kind)
 {
     if (!h || !src) return fail(HEAT_E_INVALID, "heat_upload: bad arguments");
     if ((h->p.nranks > 1 || h->p.nranks_y > 1) && !h->connected && !h->external_halo)
         return fail(HEAT_E_STATE, "heat_upload: connect the strips first");
     CK(cudaSetDevice(h->p.device));
-    const float* rows = (const float*)src + (size_t)h->lo * h->p.ny + h->lo_c;
+    int rc = quiesce_neighbours(h);
+    if (rc) return rc;
+    const float* rows = (const float*)src + (size_t)(h->lo - src_first_row) * h->p.ny + h->lo_c;
     // C:197-198: the initial field goes into both buffers -- over PCIe once, the second copy on the device
     CK(cudaMemcpy2DAsync(h->buf[0], h->pitch * sizeof(float), rows, (size_t)h->p.ny * sizeof(float),
                          (size_t)h->nyloc * sizeof(float), h->nloc, kind, h->stream));
@@ -997,8 +1091,8 @@ static int upload_from(heat_handle* h, const void* src, cudaMemcpyKind kind)
     return after_upload(h);
 }
 
-extern "C" int heat_upload(heat_handle* h, const float* full_grid) { return upload_from(h, full_grid, cudaMemcpyHostToDevice); }
-extern "C" int heat_upload_device(heat_handle* h, const void* d_full_grid) { return upload_from(h, d_full_grid, cudaMemcpyDeviceToDevice); }
+extern "C" int heat_upload(heat_handle* h, const float* full_grid) { return upload_from(h, full_grid, 0, cudaMemcpyHostToDevice); }
+extern "C" int heat_upload_device(heat_handle* h, const void* d_full_grid) { return upload_from(h, d_full_grid, 0, cudaMemcpyDeviceToDevice); }
 
 extern "C" int heat_init_inidat(heat_handle* h)
 {
@@ -1006,6 +1100,10 @@ extern "C" int heat_init_inidat(heat_handle* h)
     if ((h->p.nranks > 1 || h->p.nranks_y > 1) && !h->connected && !h->external_halo)
         return fail(HEAT_E_STATE, "heat_init_inidat: connect the strips first");
     CK(cudaSetDevice(h->p.device));
+    {
+        int rc = quiesce_neighbours(h);
+        if (rc) return rc;
+    }
     heat_inidat_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(h->buf[0], h->buf[1], h->p.nx, h->p.ny, h->lo, h->nloc, h->pitch,
                                                                h->lo_c, h->nyloc);
     h->launches++;
@@ -1017,6 +1115,10 @@ extern "C" int heat_download(heat_handle* h, float* full_grid)
 {
     if (!h || !full_grid) return fail(HEAT_E_INVALID, "heat_download: bad arguments");
     CK(cudaSetDevice(h->p.device));
+    {
+        int rc = ensure_loaded(h);
+        if (rc) return rc;
+    }
     // only the rows and columns this block owns (ghost rows/columns belong to the neighbours)
     const int first = h->row0 - h->lo, firstc = h->col0 - h->lo_c;
     CK(cudaMemcpy2DAsync(full_grid + (size_t)h->row0 * h->p.ny + h->col0, (size_t)h->p.ny * sizeof(float),
@@ -1031,8 +1133,8 @@ extern "C" int heat_upload_local(heat_handle* h, const float* local_rows)
 {
     if (!h || !local_rows) return fail(HEAT_E_INVALID, "heat_upload_local: bad arguments");
     if (h->p.nranks_y > 1) return fail(HEAT_E_STATE, "heat_upload_local: row strips only (column blocks use heat_upload)");
-    // same copy as heat_upload, whose source starts at the strip's first local row
-    return upload_from(h, local_rows - (size_t)h->lo * h->p.ny, cudaMemcpyHostToDevice);
+    // same copy as heat_upload, from a source whose first row is the strip's first local row
+    return upload_from(h, local_rows, h->lo, cudaMemcpyHostToDevice);
 }
 
 extern "C" int heat_download_local(heat_handle* h, float* own_rows)
@@ -1040,6 +1142,10 @@ extern "C" int heat_download_local(heat_handle* h, float* own_rows)
     if (!h || !own_rows) return fail(HEAT_E_INVALID, "heat_download_local: bad arguments");
     if (h->p.nranks_y > 1) return fail(HEAT_E_STATE, "heat_download_local: row strips only (column blocks use heat_download)");
     CK(cudaSetDevice(h->p.device));
+    {
+        int rc = ensure_loaded(h);
+        if (rc) return rc;
+    }
     const int first = h->row0 - h->lo;
     CK(cudaMemcpy2DAsync(own_rows, (size_t)h->p.ny * sizeof(float), h->buf[h->cur] + (size_t)first * h->pitch,
                          h->pitch * sizeof(float), (size_t)h->p.ny * sizeof(float), h->rows_own, cudaMemcpyDeviceToHost,
@@ -1059,6 +1165,126 @@ extern "C" int heat_device_view(heat_handle* h, int which, void** d_ptr, int64_t
 }
 
 // ------------------------------------------------------------------ one-shot (C:176-242)
+// heat_solve() on a host field is bound by PCIe, not by the kernels: 8 bytes per point cross the bus once in each
+// direction, against 8 bytes per point and UPDATE through HBM at ~100 times the bandwidth.  The reference does
+// H2D, loop, D2H one after the other (C:197-198, 204-238, 242).  Here the three overlap: the field arrives in
+// bands of rows on a copy stream; as soon as band i has landed, the compute stream runs ALL passes on it,
+// pass p shifted up by p*s rows (time skewing: pass p of band i covers rows [i*B - p*s, (i+1)*B - p*s), so every
+// row it reads already holds the level below, and nothing it overwrites is still needed); the rows that are final
+// after band i leave on a second copy stream while band i+1 is still arriving.  Same kernels, same two buffers,
+// same bits as the plain loop -- only the order in which (row, update) pairs are computed differs.
+// Used when there is no convergence check (an early stop needs whole-field residuals) and the total skew is
+// small against the field; HEAT_SOLVE_STREAMED=0 turns it off.
+static bool solve_can_stream(const heat_handle* h, long long updates)
+{
+#ifdef HEAT_BOUNDS_CHECK
+    return false; // the debug build's access windows are set per pass by enqueue_update
+#endif
+    if (env_int("HEAT_SOLVE_STREAMED", 1) == 0) return false;
+    if (h->p.nranks != 1 || h->p.nranks_y != 1 || h->p.conv_every > 0 || updates < 1) return false;
+    if (h->p.nx < 64 || h->p.ny < 3) return false;
+    const int T = h->p.temporal_block;
+    const long long passes = updates / T + updates % T;
+    return passes * T * 4 <= h->p.nx; // the skew costs passes*T extra rows of pipeline: keep it under a quarter
+}
+
+static int solve_streamed(heat_handle* h, float* grid, long long updates)
+{
+    const int nx = h->p.nx, ny = h->p.ny, T = h->p.temporal_block;
+    const int nfused = (int)(T > 1 ? updates / T : 0), P = (int)(T > 1 ? updates / T + updates % T : updates);
+    const int s = T;             // rows a pass is shifted against the one before: >= what a pass reads beyond its rows
+    const long long S = (long long)P * s;
+    const size_t row_bytes = (size_t)ny * sizeof(float);
+    // band height: a sixteenth of the field, between 8 and 128 MiB (small enough to fill the pipeline quickly, large
+    // enough that a pass over one band is several waves of CTAs); HEAT_SOLVE_BAND_ROWS overrides
+    size_t band_bytes = (size_t)nx * row_bytes / 16;
+    if (band_bytes < ((size_t)8 << 20)) band_bytes = (size_t)8 << 20;
+    if (band_bytes > ((size_t)128 << 20)) band_bytes = (size_t)128 << 20;
+    long long B = (long long)((band_bytes + row_bytes - 1) / row_bytes);
+    B = env_int("HEAT_SOLVE_BAND_ROWS", (int)B);
+    if (B < 2 * s) B = 2 * s;
+    if (B < 8) B = 8;
+    if (B > nx) B = nx;
+
+    CK(cudaSetDevice(h->p.device));
+    cudaStream_t in_s = nullptr, out_s = nullptr;
+    cudaEvent_t ev_in = nullptr, ev_done = nullptr;
+    int rc = HEAT_OK;
+    const int upd_lo0 = h->upd_lo, upd_hi0 = h->upd_hi;
+#define CKS(call)                                                                                                  \
+    do {                                                                                                           \
+        cudaError_t e_ = (call);                                                                                   \
+        if (e_ != cudaSuccess && !rc)                                                                              \
+            rc = fail(HEAT_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__);    \
+    } while (0)
+    CKS(cudaStreamCreateWithFlags(&in_s, cudaStreamNonBlocking));
+    CKS(cudaStreamCreateWithFlags(&out_s, cudaStreamNonBlocking));
+    CKS(cudaEventCreateWithFlags(&ev_in, cudaEventDisableTiming));
+    CKS(cudaEventCreateWithFlags(&ev_done, cudaEventDisableTiming));
+    CKS(cudaEventRecord(h->ev0, h->stream));
+    float* const fin = h->buf[P & 1]; // pass p reads buf[(p-1)&1] and writes buf[p&1]
+    long long sent = 0;               // rows [1, sent) are final and on their way to the host
+    sent = 1;
+    for (long long i = 0; !rc && sent < nx - 1; i++) {
+        const long long b0 = i * B, b1 = (i + 1) * B < nx ? (i + 1) * B : nx;
+        if (b0 < nx) { // a real band: rows [b0, b1) arrive in buf[0]
+            CKS(cudaMemcpy2DAsync(h->buf[0] + b0 * h->pitch, h->pitch * sizeof(float), grid + b0 * ny, row_bytes, row_bytes,
+                                  (size_t)(b1 - b0), cudaMemcpyHostToDevice, in_s));
+            CKS(cudaEventRecord(ev_in, in_s));
+            CKS(cudaStreamWaitEvent(h->stream, ev_in, 0));
+            // the ring rows never change: buf[1] needs its own copy of them (C:197-198 uploads the field twice)
+            if (b0 == 0) CKS(cudaMemcpyAsync(h->buf[1], h->buf[0], row_bytes, cudaMemcpyDeviceToDevice, h->stream));
+            if (b1 == nx)
+                CKS(cudaMemcpyAsync(h->buf[1] + (size_t)(nx - 1) * h->pitch, h->buf[0] + (size_t)(nx - 1) * h->pitch, row_bytes,
+                                    cudaMemcpyDeviceToDevice, h->stream));
+        }
+        for (int p = 1; p <= P && !rc; p++) {
+            long long lo = b0 - (long long)p * s, hi = b0 + B - (long long)p * s;
+            if (lo < 1) lo = 1;
+            if (hi > nx - 1) hi = nx - 1;
+            if (lo >= hi) continue;
+            h->upd_lo = (int)lo;
+            h->upd_hi = (int)hi;
+            const float* in = h->buf[(p - 1) & 1];
+            float* out = h->buf[p & 1];
+            if (p <= nfused) CKS(launch_tb(h, T, in, out, nullptr, nullptr, 0));
+            else CKS(launch_step(h, false, in, out, nullptr, nullptr, 0));
+        }
+        long long done = b0 + B - S; // rows below this are final now
+        if (done > nx - 1) done = nx - 1;
+        if (done > sent) {
+            CKS(cudaEventRecord(ev_done, h->stream));
+            CKS(cudaStreamWaitEvent(out_s, ev_done, 0));
+            CKS(cudaMemcpy2DAsync(grid + sent * ny, row_bytes, fin + sent * h->pitch, h->pitch * sizeof(float), row_bytes,
+                                  (size_t)(done - sent), cudaMemcpyDeviceToHost, out_s));
+            sent = done;
+        }
+    }
+#undef CKS
+    h->upd_lo = upd_lo0;
+    h->upd_hi = upd_hi0;
+    if (!rc && cudaEventRecord(h->ev1, h->stream) != cudaSuccess) rc = fail(HEAT_E_CUDA, "cudaEventRecord failed");
+    // always drain the three streams before they go away (also after an error)
+    cudaError_t e1 = in_s ? cudaStreamSynchronize(in_s) : cudaSuccess;
+    cudaError_t e2 = cudaStreamSynchronize(h->stream);
+    cudaError_t e3 = out_s ? cudaStreamSynchronize(out_s) : cudaSuccess;
+    if (!rc && (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess))
+        rc = fail(HEAT_E_CUDA, "heat_solve (streamed): %s", cudaGetErrorString(e1 != cudaSuccess ? e1 : e2 != cudaSuccess ? e2 : e3));
+    if (!rc) {
+        cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+        h->cur = P & 1;
+        h->it += updates;
+        h->sweeps += P;
+        h->loaded = true;
+    }
+    if (ev_in) cudaEventDestroy(ev_in);
+    if (ev_done) cudaEventDestroy(ev_done);
+    if (in_s) cudaStreamDestroy(in_s);
+    if (out_s) cudaStreamDestroy(out_s);
+    cudaGetLastError();
+    return rc;
+}
+
 extern "C" int heat_solve(const heat_params* p, float* grid, int* updates_done, int* converged)
 {
     if (!grid) return fail(HEAT_E_INVALID, "heat_solve: null grid");
@@ -1075,17 +1301,33 @@ extern "C" int heat_solve(const heat_params* p, float* grid, int* updates_done, 
     int rc = heat_create(p, &h);
     if (rc) return rc;
     const double t1 = now();
-    rc = heat_upload(h, grid);
-    const double t2 = now();
-    if (!rc) rc = heat_run(h, p->steps, updates_done, converged);
-    const double t3 = now();
-    if (!rc) rc = heat_download(h, grid);
-    const double t4 = now();
+    const long long total = (long long)p->steps + (p->step_convention == HEAT_STEPS_MPI ? 1 : 0);
+    double t2, t3, t4;
+    const bool streamed = solve_can_stream(h, total);
+    if (streamed) {
+        rc = solve_streamed(h, grid, total);
+        if (!rc) {
+            if (updates_done) *updates_done = (int)total;
+            if (converged) *converged = 0;
+        }
+        t2 = t1, t3 = t4 = now();
+    } else {
+        rc = heat_upload(h, grid);
+        t2 = now();
+        if (!rc) rc = heat_run(h, p->steps, updates_done, converged);
+        t3 = now();
+        if (!rc) rc = heat_download(h, grid);
+        t4 = now();
+    }
     const float loop_ms = h->last_ms;
+    char keep[sizeof g_err];
+    memcpy(keep, g_err, sizeof keep); // heat_destroy must not hide the first error
     heat_destroy(h);
+    if (rc) memcpy(g_err, keep, sizeof keep);
     if (timing)
-        fprintf(stderr, "heat_solve: create %.3f ms, upload %.3f ms, run %.3f ms (device loop %.3f ms), download %.3f ms, destroy %.3f ms\n",
-                (t1 - t0) * 1e3, (t2 - t1) * 1e3, (t3 - t2) * 1e3, loop_ms, (t4 - t3) * 1e3, (now() - t4) * 1e3);
+        fprintf(stderr, "heat_solve%s: create %.3f ms, upload %.3f ms, run %.3f ms (device loop %.3f ms), download %.3f ms, destroy %.3f ms\n",
+                streamed ? " (streamed: upload, loop and download overlap inside `run`)" : "", (t1 - t0) * 1e3, (t2 - t1) * 1e3,
+                (t3 - t2) * 1e3, loop_ms, (t4 - t3) * 1e3, (now() - t4) * 1e3);
     return rc;
 }
 
@@ -1124,7 +1366,10 @@ static int step_device(const void* d_in, void* d_out, int nx, int ny, float cx, 
     if (!d_in || !d_out || nx < 1 || ny < 1 || arith < 0 || arith > 2 || (RESID && !resid))
         return fail(HEAT_E_INVALID, "heat_step_device: bad arguments");
     if (nx < 3 || ny < 3) return HEAT_OK;
-    dim3 grid((unsigned)((ny - 2 + 255) / 256), (unsigned)min(nx - 2, 148 * 8));
+    int dev = 0, sms = 0;
+    CK(cudaGetDevice(&dev));
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)); // a cached driver attribute: no device round trip
+    dim3 grid((unsigned)((ny - 2 + 255) / 256), (unsigned)min(nx - 2, sms * 8));
     const float* in = (const float*)d_in;
     float* out = (float*)d_out;
     cudaStream_t st = (cudaStream_t)stream;

@@ -218,16 +218,18 @@ __device__ __forceinline__ void strip_signal(const strip_sync& sy, bool edge_n, 
         __syncthreads(); // every thread's stores (local and peer) are issued
         if (threadIdx.x == 0) {
             // Row neighbours: a handful of edge CTAs, each fences at system scope before it counts itself.
-            // Column neighbours: one edge CTA per tile row (thousands); they fence at GPU scope only and the
-            // CTA that arrives last issues the one system-scope fence -- the release is cumulative over the
-            // arrivals it observed through the counter.
+            // Column neighbours: one edge CTA per tile row (thousands); they fence at GPU scope only.  On every
+            // side the CTA that arrives last fences at system scope BEHIND its ticket (fence-atomic ... atomic-fence
+            // is the PTX model's release/acquire pattern), then releases the flag.
             if (e[0] || e[1]) __threadfence_system();
             else __threadfence();
 #pragma unroll
             for (int k = 0; k < 4; k++)
                 if (e[k] && atomicAdd(&sy.counters[k], 1u) == sy.count[k] - 1) {
+                    // last arrival: the fence behind the (relaxed) ticket makes this an acquire of every earlier
+                    // arrival's fence + ticket, so their peer stores are ordered before the flag for the neighbour
+                    __threadfence_system();
                     sy.counters[k] = 0;
-                    if (k >= 2) __threadfence_system();
                     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(sy.sig[k]), "l"(sy.sig_value) : "memory");
                 }
         }
@@ -852,34 +854,16 @@ __global__ void heat_signal(unsigned long long* peer_flag_n, unsigned long long*
     }
 }
 
-// Before update u+1 a strip waits until both neighbours have finished update u.
+// Before update u+1 a strip waits until its neighbours have finished update u (also used before an upload
+// overwrites a strip whose neighbours may still be storing ghost rows into it).
 // Bounded: after timeout_ns the kernel gives up and raises *status (checked by the host).
-__global__ void heat_wait(const unsigned long long* flag_n, const unsigned long long* flag_s, unsigned long long value,
-                          unsigned long long timeout_ns, int* status)
+__global__ void heat_wait(const unsigned long long* flag_n, const unsigned long long* flag_s, const unsigned long long* flag_w,
+                          const unsigned long long* flag_e, unsigned long long value, unsigned long long timeout_ns, int* status)
 {
     if (threadIdx.x != 0) return;
-    unsigned long long t0;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-    for (int side = 0; side < 2; side++) {
-        const unsigned long long* f = side ? flag_s : flag_n;
-        if (!f) continue;
-        unsigned spins = 0;
-        for (;;) {
-            unsigned long long v;
-            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
-            if (v >= value) break;
-            if ((++spins & 1023u) == 0) {
-                unsigned long long t;
-                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-                if (t - t0 > timeout_ns) {
-                    *status = 1;
-                    __threadfence_system();
-                    return;
-                }
-            }
-            __nanosleep(64);
-        }
-    }
+    const unsigned long long* f[4] = {flag_n, flag_s, flag_w, flag_e};
+    for (int side = 0; side < 4; side++)
+        if (f[side]) spin_until(f[side], value, timeout_ns, status);
 }
 
 } // namespace heatk

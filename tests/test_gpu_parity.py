@@ -270,6 +270,57 @@ def test_unconnected_strip_refuses_to_run(ph):
         assert ei.value.code == ph.api.E_STATE
 
 
+# ---------------------------------------------------------------- heat_solve: upload, loop and download overlapped
+@pytest.mark.parametrize("T", [1, 2, 4])
+@pytest.mark.parametrize("arith", MODES)
+def test_streamed_solve_is_bit_identical(ph, oracle, T, arith, monkeypatch):
+    # heat_solve() streams the field through the GPU in bands of rows, pass p shifted up by p*T rows (time
+    # skewing): only the ORDER of (row, update) pairs changes, so the bits must be those of the plain loop.
+    # Band heights that do and do not divide the field, shorter than the total skew, a single band.
+    for shape, steps in [((300, 517), 1), ((300, 517), 7), ((1000, 260), 20), ((2050, 140), 40), ((64, 64), 16), ((777, 33), 9)]:
+        u = field(shape, seed=shape[0] + steps)
+        want, _, _ = oracle.solve(u, steps, arith=arith)
+        for band in (0, 8, 13, 64, 5000):
+            if band:
+                monkeypatch.setenv("HEAT_SOLVE_BAND_ROWS", str(band))
+            else:
+                monkeypatch.delenv("HEAT_SOLVE_BAND_ROWS", raising=False)
+            got, done, conv = ph.solve(u, steps, arith=arith, temporal_block=T)
+            assert (done, conv) == (steps, False)
+            assert_same_bits(got, want, f"streamed {shape} steps={steps} T={T} band={band} arith={arith}")
+    monkeypatch.delenv("HEAT_SOLVE_BAND_ROWS", raising=False)
+    # and the same call with streaming switched off is the same field
+    u = field((1000, 260), seed=5)
+    a, _, _ = ph.solve(u, 20, arith=arith, temporal_block=T)
+    monkeypatch.setenv("HEAT_SOLVE_STREAMED", "0")
+    b, _, _ = ph.solve(u, 20, arith=arith, temporal_block=T)
+    assert_same_bits(a, b, "streamed vs plain")
+
+
+def test_streamed_solve_mpi_step_convention_and_ring(ph, oracle):
+    # `steps`+1 updates (M:159) through the streamed path; a non-zero ring must come back untouched
+    u = field((512, 300), seed=11)
+    want, wdone, _ = oracle.solve(u, 30, arith=2, step_convention=1)
+    got, done, _ = ph.solve(u, 30, arith=2, step_convention=ph.STEPS_MPI)
+    assert done == wdone == 31
+    assert_same_bits(got, want, "streamed, MPI step convention")
+    assert_same_bits(got[[0, -1]], u[[0, -1]], "ring rows")
+    assert_same_bits(got[:, [0, -1]], u[:, [0, -1]], "ring columns")
+
+
+def test_streamed_solve_8192(ph, oracle):
+    # BASELINE config[1]'s grid through heat_solve with the bench's step count: windows against the oracle
+    n, k = 8192, 20
+    got, done, _ = ph.solve(ph.inidat(n, n), k)
+    assert done == k
+    ini = oracle.inidat(n, n)
+    for r0 in (0, 500, 4090, n - 60):
+        band = 60
+        lo, hi = max(0, r0 - k), min(n, r0 + band + k)
+        want, _, _ = oracle.solve(ini[lo:hi], k, arith=0)
+        assert_same_bits(got[r0:r0 + band], want[r0 - lo:r0 - lo + band], f"8192^2 streamed rows {r0}..")
+
+
 # ---------------------------------------------------------------- K4: temporal blocking
 @pytest.mark.parametrize("T", [2, 4])
 @pytest.mark.parametrize("arith", MODES)

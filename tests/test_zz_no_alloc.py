@@ -45,6 +45,28 @@ def test_two_calls_in_a_row_match_the_ordinary_entry_point(ph, arith):
             src_new, src_old = out_new, out_old  # second call: feed the first call's result back in
 
 
+@pytest.mark.parametrize("arith", [0, 1, 2])
+def test_field_and_residual_match_the_cpu_oracle(ph, oracle, arith):
+    # the same entry point against the CPU restatement of the reference's update (M:168-174 / C:155-161) and of
+    # its convergence quantity max|old-new| (M:245, C:67) -- so this file does not lean on any other GPU path
+    import torch
+    for shape in [(20, 20), (33, 47), (300, 1030)]:
+        nx, ny = shape
+        u = (np.random.default_rng(7 * nx + ny).standard_normal(shape) * 1e3).astype(np.float32)
+        want = oracle.step(u, arith=arith, out=np.full(shape, -3.0, np.float32))
+        inner = (slice(1, -1), slice(1, -1))
+        want_res = oracle.max_abs_diff(np.ascontiguousarray(u[inner]), np.ascontiguousarray(want[inner]))
+        d_in = torch.from_numpy(u).cuda()
+        d_out = torch.full(shape, -3.0, device="cuda")
+        res = torch.full((1,), 123.0, device="cuda")
+        for call in range(2):
+            ph.api.step_residual_noalloc(d_in.data_ptr(), d_out.data_ptr(), nx, ny, res.data_ptr(), arith=arith,
+                                         stream=torch.cuda.current_stream().cuda_stream)
+            torch.cuda.synchronize()
+            assert np.array_equal(bits(d_out.cpu().numpy()), bits(want)), (shape, call, "field vs oracle")
+            assert res.cpu().numpy().view(np.uint32)[0] == np.float32(want_res).view(np.uint32), (shape, call, "residual vs oracle")
+
+
 def test_no_interior_gives_zero_residual(ph):
     import torch
     u = torch.ones((2, 9), device="cuda")
