@@ -155,6 +155,18 @@ class ClockSampler:
             self._t.join()
             self._t = None
 
+    def nvlink_kib(self):
+        """(tx, rx) KiB moved over all NVLinks of this GPU so far (NVML field values), or None."""
+        nv = self.nv
+        try:
+            v = nv.nvmlDeviceGetFieldValues(self.h, [(nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, 0xFFFFFFFF),
+                                                     (nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX, 0xFFFFFFFF)])
+            if v[0].nvmlReturn != 0 or v[1].nvmlReturn != 0:
+                return None
+            return int(v[0].value.ullVal), int(v[1].value.ullVal)
+        except Exception:
+            return None
+
     def window(self, t0, t1):
         """Summary of the samples taken in [t0, t1] (host clock); the nearest one if the region was too short."""
         inside = [s for s in self.samples if t0 <= s[0] <= t1]
@@ -330,7 +342,7 @@ class Ctx:
             self.torch.cuda.synchronize()
 
 
-def measure(ctx, enqueue, sync, K, W, reps=None, launch_count=lambda: 0):
+def measure(ctx, enqueue, sync, K, W, reps=None, launch_count=lambda: 0, before_barrier=None, after_timed=None):
     """The timing scheme of the module docstring.  Returns a dict with the per-repetition times (max over ranks)."""
     torch = ctx.torch
     ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
@@ -347,6 +359,8 @@ def measure(ctx, enqueue, sync, K, W, reps=None, launch_count=lambda: 0):
         warm_ms = float(t.item())
     R = reps or int(min(MAX_REPS, max(MIN_REPS, math.ceil(TARGET_REGION_MS / max(warm_ms, 1e-3)))))
     events = [ev() for _ in range(R + 1)]
+    if before_barrier:
+        before_barrier()
     ctx.barrier()
     enqueue(LOCKSTEP_UPDATES)  # neighbours wait for each other's flags here, not inside the first repetition
     n0 = launch_count()
@@ -358,6 +372,7 @@ def measure(ctx, enqueue, sync, K, W, reps=None, launch_count=lambda: 0):
     sync()
     t1 = time.perf_counter()
     n1 = launch_count()
+    extra = after_timed() if after_timed else None
     ctx.barrier()
     mine = [events[r].elapsed_time(events[r + 1]) for r in range(R)]
     per_rank_median = [sorted(mine)[R // 2]]
@@ -373,7 +388,7 @@ def measure(ctx, enqueue, sync, K, W, reps=None, launch_count=lambda: 0):
     s = sorted(times)
     return {"reps": R, "K": K, "median_ms": s[R // 2], "best_ms": s[0], "worst_ms": s[-1], "mean_ms": sum(times) / R,
             "per_rank_median_ms": per_rank_median, "warm_rep_ms": warm_ms, "clocks": ctx.clocks.window(t0, t1),
-            "host_secs": t1 - t0, "launches": n1 - n0}
+            "host_secs": t1 - t0, "launches": n1 - n0, "extra": extra}
 
 
 def device_window(torch, ptr, pitch, r0, r1, c0, c1, device):
@@ -433,6 +448,8 @@ def run_one(ctx, api, wl, arith, args):
     T = wl["temporal_block"]
     params = dict(arith=arith, conv_every=wl["conv_every"], temporal_block=T)
     s = None
+    if args.k3_profile:
+        os.environ["HEAT_PROFILE_WAIT"] = "1"  # read by heat_create: the edge CTAs time their flag waits
     if world > 1:
         from parallel_heat_b200.strips import StripSolver
         s = StripSolver(nx, ny, device=ctx.local_rank, halo=args.halo, cols=args.cols, **params)
@@ -457,7 +474,19 @@ def run_one(ctx, api, wl, arith, args):
             # the convergence-check loop is host-driven every conv_every updates: time heat_run itself
             def enqueue(n):  # noqa: F811
                 solver.run(n)
-        m = measure(ctx, enqueue, sync, K, W, reps=args.reps or None, launch_count=solver.launch_count)
+        k3 = {}
+
+        def k3_begin():
+            if args.k3_profile and world > 1:
+                solver.wait_stats()  # clears the counters (synchronises the stream: before the barrier, not after)
+                k3["nvl0"] = ctx.clocks.nvlink_kib()
+
+        def k3_end():
+            if args.k3_profile and world > 1:
+                k3["nvl1"] = ctx.clocks.nvlink_kib()
+                k3["wait"] = solver.wait_stats()
+        m = measure(ctx, enqueue, sync, K, W, reps=args.reps or None, launch_count=solver.launch_count,
+                    before_barrier=k3_begin, after_timed=k3_end)
         launches = m["launches"]  # this rank's kernel launches between the first and the last timed event
         ms = m["median_ms"]
         lups_per_update = (nx - 2) * (ny - 2)
@@ -488,7 +517,9 @@ def run_one(ctx, api, wl, arith, args):
 
             def get(r0, r1, c0, c1):
                 return device_window(torch, ptr, pitch, r0 - lo, r1 - lo, c0 - lo_c, c1 - lo_c, ctx.local_rank)
-            nw, npts, nbad = parity_windows(ctx, wl, arith, (lo, nloc, lo_c, hi_c - lo_c), U, get)
+            # 2-D blocks keep their ghost COLUMNS in dense side arrays, not in the field: owned columns only there
+            vc0, vc1 = (s.col0, s.col0 + s.ncols) if (world > 1 and args.cols > 1) else (lo_c, hi_c)
+            nw, npts, nbad = parity_windows(ctx, wl, arith, (lo, nloc, vc0, vc1 - vc0), U, get)
             if world > 1:
                 t = torch.tensor([nw, npts, nbad], device="cuda", dtype=torch.float64)
                 dist.all_reduce(t)
@@ -496,7 +527,29 @@ def run_one(ctx, api, wl, arith, args):
             parity = {"windows": nw, "points": npts, "mismatches": nbad, "bit_exact": nbad == 0, "updates": U,
                       "against": "oracle.solve on each window + margin (40x64 windows: strip boundaries incl. ghost rows, "
                                  "middle, field edges), after re-initialising and running the same enqueue path"}
-        out = {"value": value, "unit": "GLUP/s", "ms_per_step": ms / K, "steps": K, "reps": m["reps"],
+        k3_out = None
+        if args.k3_profile and world > 1:
+            # K3 evidence, per rank: how long the edge CTAs waited for the neighbours' flags and what went over NVLink
+            passes = (m["reps"] * K + LOCKSTEP_UPDATES) // T
+            ns, cnt = k3["wait"]
+            mine = [float(ctx.rank), ms / max(step_launches, 1) * 1e3] + [float(x) / max(passes, 1) / 1e3 for x in ns[:2]] + \
+                   [float(x) / max(passes, 1) for x in cnt[:2]]
+            if k3.get("nvl0") and k3.get("nvl1"):
+                mine += [(k3["nvl1"][0] - k3["nvl0"][0]) / max(passes, 1), (k3["nvl1"][1] - k3["nvl0"][1]) / max(passes, 1)]
+            else:
+                mine += [-1.0, -1.0]
+            g = torch.zeros((world, len(mine)), device="cuda", dtype=torch.float64)
+            g[ctx.rank] = torch.tensor(mine, dtype=torch.float64)
+            dist.all_reduce(g)
+            k3_out = {"per_rank": [{"rank": int(r[0]), "pass_us": r[1], "edge_wait_us_per_pass_north": r[2],
+                                    "edge_wait_us_per_pass_south": r[3], "edge_waits_per_pass_north": r[4],
+                                    "edge_waits_per_pass_south": r[5], "nvlink_tx_kib_per_pass": r[6], "nvlink_rx_kib_per_pass": r[7]}
+                                   for r in g.tolist()],
+                      "note": "edge_wait = SUM over the edge CTAs of one pass of the time their thread 0 spun on the neighbour's step "
+                              "flag (globaltimer; a pass has edge_waits CTAs that wait, the other CTAs never do); nvlink = NVML "
+                              "NVLINK_THROUGHPUT_DATA counters over the timed region / passes (ghost rows + flags; expected "
+                              f"{T * ny * 4 / 1024:.0f} KiB per neighbour and pass)"}
+        out = {"value": value, "unit": "GLUP/s", "ms_per_step": ms / K, "steps": K, "reps": m["reps"], "k3": k3_out,
                "rep_ms": {"best": m["best_ms"], "median": m["median_ms"], "worst": m["worst_ms"], "mean": m["mean_ms"]},
                "per_rank_median_ms": m["per_rank_median_ms"], "roofline": roofline, "clocks": m["clocks"],
                "gpu_launches": int(launches), "parity": parity}
@@ -680,7 +733,7 @@ def run_ours(args, wl, rank, world, local_rank):
                "dtype": "f32" if arith != api.MPI_F64MIX else "f32 grid, f64-mixed arithmetic", "data": "synthetic",
                "config": cfg, "reps": main["reps"], "rep_ms": main["rep_ms"], "per_rank_median_ms": main["per_rank_median_ms"],
                "roofline": main["roofline"], "cpu_baseline": base, "e2e": e2e, "gpu_launches": main["gpu_launches"],
-               "clocks": main["clocks"], "parity": main["parity"], "also": also}
+               "clocks": main["clocks"], "parity": main["parity"], "k3": main.get("k3"), "also": also}
         print(json.dumps(out), flush=True)
     bad = main["parity"] is not None and not main["parity"]["bit_exact"]
     if e2e and e2e.get("parity") and not e2e["parity"]["bit_exact"]:
@@ -705,6 +758,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-also", action="store_true", help="skip the other 1-GPU configurations")
+    ap.add_argument("--k3-profile", action="store_true", help="N>1: per-rank edge-CTA flag-wait time and NVLink bytes per pass")
     ap.add_argument("--no-parity", action="store_true", help="skip the bit-exact window check after the timed region")
     args = ap.parse_args()
 

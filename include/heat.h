@@ -224,6 +224,11 @@ int heat_group_enqueue(heat_handle **strips, int n, int updates);
 /* Convergence across strips in OTHER processes: every conv_every updates heat_run hands the
  * local max|old-new| to this callback, which must return the maximum over all strips in
  * *value (one 4-byte max-allreduce; replaces MPI_Allreduce(LAND), M:255).  Return 0 on success. */
+/* Diagnostics (handle created with HEAT_PROFILE_WAIT=1 in the environment, else HEAT_E_STATE): nanoseconds the
+ * edge CTAs of this strip's update kernels spent waiting for each neighbour's step flag (sides: north, south,
+ * west, east) and the number of such waits, since the previous call.  The evidence behind "interior tiles never
+ * wait" (replaces reading MPI_Waitall time off a profiler, M:177). */
+int heat_debug_wait_stats(heat_handle *h, unsigned long long *ns_per_side, unsigned long long *waits_per_side);
 typedef int (*heat_allreduce_max_fn)(float *value, void *ctx);
 int heat_set_allreduce_max(heat_handle *h, heat_allreduce_max_fn fn, void *ctx);
 

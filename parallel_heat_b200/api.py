@@ -90,6 +90,7 @@ SIGNATURES = {
     "heat_group_run": (C.c_int, [C.POINTER(_H), C.c_int, C.c_int, _ip, _ip]),
     "heat_group_enqueue": (C.c_int, [C.POINTER(_H), C.c_int, C.c_int]),
     "heat_set_allreduce_max": (C.c_int, [_H, ALLREDUCE_FN, C.c_void_p]),
+    "heat_debug_wait_stats": (C.c_int, [_H, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]),
 }
 
 _lib = None
@@ -293,6 +294,12 @@ class HeatSolver:
 
     def connect_local(self, north, south, west=None, east=None):
         _check(load().heat_connect_local2d(self._h, *[o._h if o else None for o in (north, south, west, east)]))
+
+    def wait_stats(self):
+        """(ns waited per side, waits per side) of the edge CTAs since the last call; needs HEAT_PROFILE_WAIT=1."""
+        ns, cnt = (C.c_ulonglong * 4)(), (C.c_ulonglong * 4)()
+        _check(load().heat_debug_wait_stats(self._h, ns, cnt))
+        return list(ns), list(cnt)
 
     def set_allreduce_max(self, fn):
         """fn(value: float) -> float, the maximum over every strip's value."""

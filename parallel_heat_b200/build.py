@@ -60,8 +60,21 @@ def build(force=False, verbose=False):
     return LIB
 
 
+def build_variant(name, defines):
+    """libheat_b200_<name>.so with extra -D switches: A/B runs of one kernel decision on the GPU box
+    (HEAT_B200_LIB=<path> makes api.py, the tests and bench.py load it instead of the product library)."""
+    out = PKG / f"libheat_b200_{name}.so"
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    cmd = [nvcc, *NVCC_FLAGS, *defines, "-I", str(INCLUDE), "-o", str(out), *map(str, sources()), "-ccbin", "/usr/bin/g++"]
+    subprocess.run(cmd, check=True)
+    return out
+
+
 if __name__ == "__main__":
-    if "--debug" in sys.argv:
+    if "--variant" in sys.argv:
+        k = sys.argv.index("--variant")
+        print(build_variant(sys.argv[k + 1], [a for a in sys.argv[k + 2:] if a.startswith("-D")]))
+    elif "--debug" in sys.argv:
         print(build_debug())
     else:
         print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -197,6 +197,7 @@ struct peer_side {
     unsigned long long* flag = nullptr;   // neighbour's flag slot that this strip writes
     int nloc = 0, nyloc = 0;
     int64_t pitch = 0;
+    float* gcol = nullptr;                 // neighbour's dense ghost-column arrays (2-D blocks), see heat_handle::gcol
     void* ipc_base[3] = {nullptr, nullptr, nullptr}; // bases opened with cudaIpcOpenMemHandle
 };
 
@@ -230,15 +231,20 @@ struct heat_handle {
     bool loaded = false;          // a field has been uploaded / initialised (else the first use zero-fills)
     // neighbours: side 0 = north (lower rows), 1 = south, 2 = west (lower columns), 3 = east
     unsigned* d_edge_count = nullptr;    // [4] edge-CTA arrival counters of the fused strip ordering, per side
+    unsigned long long* d_wait_prof = nullptr; // HEAT_PROFILE_WAIT=1: [8] ns waited / waits per side (heat_debug_wait_stats)
     strip_sync sync_args = {};           // filled per pass for flag-ordered strips, else all null
     col_peers col_args = {};             // 2-D blocks: where my first / last owned column goes
     unsigned long long* flags = nullptr; // [0] written by the north neighbour, [1] south, [2] west, [3] east
+    // 2-D blocks: dense ghost columns [buffer][side: 0 west, 1 east][local row], GCOL_OFFSET bytes behind the
+    // flags in the same allocation (so one IPC handle exports both)
+    float* gcol = nullptr;
     peer_side peer[4];
     bool connected = false;
     // neighbours in this process are ordered with events instead of flags (no spinning kernels)
     heat_handle* local_nb[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev_done[2] = {nullptr, nullptr}; // recorded after epoch e in ev_done[e & 1]
     bool serpentine = true;
+    bool k1_bulk = false; // HEAT_K1_VARIANT=bulk: the shared-memory staged variant of K1 (for measurements)
     int cols_first = 0; // HEAT_COLS_FIRST = M: column-edge CTAs ahead of the rest, M tile rows each (2-D blocks across processes)
     // CUDA graphs of GRAPH_PASSES consecutive passes, one per (newest buffer, sweep direction, fused?)
     cudaGraphExec_t graphs[2][2][2] = {};
@@ -264,6 +270,8 @@ struct ipc_blob {
     int64_t pitch;
 };
 static_assert(sizeof(ipc_blob) <= HEAT_IPC_BLOB_BYTES, "ipc blob too large");
+
+static const size_t GCOL_OFFSET = 256; // bytes between the four flags and the dense ghost-column arrays
 
 static int env_int(const char* k, int dflt)
 {
@@ -309,6 +317,7 @@ extern "C" int heat_destroy(heat_handle* h)
     if (h->flags) cudaFree(h->flags);
     if (h->d_resid) cudaFree(h->d_resid);
     if (h->d_edge_count) cudaFree(h->d_edge_count);
+    if (h->d_wait_prof) cudaFree(h->d_wait_prof);
     if (h->res_halo) cudaFree(h->res_halo);
     if (h->res_flags) cudaFree(h->res_flags);
     if (h->h_resid) cudaFreeHost(h->h_resid);
@@ -374,7 +383,9 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     } while (0)
     CKH(cudaMalloc((void**)&h->buf[0], bytes));
     CKH(cudaMalloc((void**)&h->buf[1], bytes));
-    CKH(cudaMalloc((void**)&h->flags, 4 * sizeof(unsigned long long)));
+    const size_t flag_bytes = GCOL_OFFSET + (p->nranks_y > 1 ? 4 * (size_t)h->nloc * sizeof(float) : 0);
+    CKH(cudaMalloc((void**)&h->flags, flag_bytes));
+    if (p->nranks_y > 1) h->gcol = (float*)((char*)h->flags + GCOL_OFFSET);
     CKH(cudaMalloc((void**)&h->d_resid, sizeof(unsigned)));
     CKH(cudaMalloc((void**)&h->d_edge_count, 4 * sizeof(unsigned)));
     CKH(cudaHostAlloc((void**)&h->h_resid, sizeof(unsigned), cudaHostAllocDefault));
@@ -389,9 +400,13 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
         for (int k = 0; k < 2; k++)
             CKH(cudaMemset2DAsync(h->buf[k] + h->nyloc, h->pitch * sizeof(float), 0, (size_t)(h->pitch - h->nyloc) * sizeof(float),
                                   h->nloc, h->stream));
-    CKH(cudaMemsetAsync(h->flags, 0, 4 * sizeof(unsigned long long), h->stream));
+    CKH(cudaMemsetAsync(h->flags, 0, flag_bytes, h->stream));
     CKH(cudaMemsetAsync(h->d_resid, 0, sizeof(unsigned), h->stream));
     CKH(cudaMemsetAsync(h->d_edge_count, 0, 4 * sizeof(unsigned), h->stream));
+    if (env_int("HEAT_PROFILE_WAIT", 0) != 0) {
+        CKH(cudaMalloc((void**)&h->d_wait_prof, 8 * sizeof(unsigned long long)));
+        CKH(cudaMemsetAsync(h->d_wait_prof, 0, 8 * sizeof(unsigned long long), h->stream));
+    }
     CKH(cudaEventCreate(&h->ev0));
     CKH(cudaEventCreate(&h->ev1));
     CKH(cudaEventCreateWithFlags(&h->ev_resid, cudaEventDisableTiming));
@@ -403,6 +418,10 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     h->rows_per_tile = env_int("HEAT_ROWS_PER_TILE", 0);
     h->rows_per_tile_tb = env_int("HEAT_ROWS_PER_TILE_TB", 0);
     h->serpentine = env_int("HEAT_SERPENTINE", 1) != 0;
+    {
+        const char* v = getenv("HEAT_K1_VARIANT");
+        h->k1_bulk = v && !strcmp(v, "bulk");
+    }
     h->cols_first = env_int("HEAT_COLS_FIRST", 0);
     if (h->cols_first < 0) h->cols_first = 0;
 #ifdef HEAT_BOUNDS_CHECK
@@ -484,7 +503,12 @@ static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, fl
         heat_step_vec<ARITH, RESID, THREADS, UNROLL, true><<<grid, THREADS, 0, h->stream>>>(
             in, out, h->upd_lo, h->upd_hi, ny, h->pitch, rpt, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse,
             h->sync_args);
-    else
+    else if (!RESID && h->k1_bulk && !peer_n && !peer_s) {
+        constexpr int ROWS = 8;
+        dim3 g((unsigned)((h->pitch / 4 + THREADS - 1) / THREADS), (unsigned)((rows + ROWS - 1) / ROWS));
+        heat_step_bulk<ARITH, ROWS, THREADS><<<g, THREADS, 0, h->stream>>>(in, out, h->upd_lo, h->upd_hi, ny, h->pitch, h->p.cx, h->p.cy,
+                                                                          reverse, h->d_status);
+    } else
         heat_step_vec<ARITH, RESID, THREADS, UNROLL, false><<<grid, THREADS, 0, h->stream>>>(
             in, out, h->upd_lo, h->upd_hi, ny, h->pitch, rpt, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse,
             h->sync_args);
@@ -597,13 +621,15 @@ static int enqueue_update(heat_handle* h, bool resid, int fused = 1)
         if (has[0]) pn = h->peer[0].buf[1 - h->cur] + (int64_t)(h->peer[0].nloc - h->ghost) * h->pitch;
         if (has[1]) ps = h->peer[1].buf[1 - h->cur];
         // my first owned column is the west neighbour's last (ghost) column, my last its first
+        // (dense arrays, one float per local row; column neighbours have my rows: [buffer][side][row])
+        const int64_t n = h->nloc;
         if (has[2]) {
-            h->col_args.w = h->peer[2].buf[1 - h->cur] + (h->peer[2].nyloc - 1);
-            h->col_args.pitch_w = h->peer[2].pitch;
+            h->col_args.w = h->peer[2].gcol + ((1 - h->cur) * 2 + 1) * n; // its EAST ghost, new buffer
+            h->col_args.gw_in = h->gcol + (h->cur * 2 + 0) * n;
         }
         if (has[3]) {
-            h->col_args.e = h->peer[3].buf[1 - h->cur];
-            h->col_args.pitch_e = h->peer[3].pitch;
+            h->col_args.e = h->peer[3].gcol + ((1 - h->cur) * 2 + 0) * n; // its WEST ghost, new buffer
+            h->col_args.ge_in = h->gcol + (h->cur * 2 + 1) * n;
         }
     }
     if (resid) CK(cudaMemsetAsync(h->d_resid, 0, sizeof(unsigned), h->stream));
@@ -620,6 +646,7 @@ static int enqueue_update(heat_handle* h, bool resid, int fused = 1)
         sy.counters = h->d_edge_count;
         sy.status = h->d_status;
         sy.timeout_ns = WAIT_TIMEOUT_NS;
+        sy.prof = h->d_wait_prof;
     }
 #ifdef HEAT_BOUNDS_CHECK
     {
@@ -1003,6 +1030,21 @@ extern "C" int heat_launch_count(heat_handle* h, int64_t* launches)
     return HEAT_OK;
 }
 
+// Diagnostics of the fused strip ordering (created with HEAT_PROFILE_WAIT=1 in the environment): how long the edge
+// CTAs of this strip's update kernels have spun on each neighbour's flag since the last call, and how often.
+extern "C" int heat_debug_wait_stats(heat_handle* h, unsigned long long* ns_per_side, unsigned long long* waits_per_side)
+{
+    if (!h || !ns_per_side || !waits_per_side) return fail(HEAT_E_INVALID, "heat_debug_wait_stats: bad arguments");
+    if (!h->d_wait_prof) return fail(HEAT_E_STATE, "heat_debug_wait_stats: create the handle with HEAT_PROFILE_WAIT=1");
+    CK(cudaSetDevice(h->p.device));
+    unsigned long long v[8];
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaMemcpy(v, h->d_wait_prof, sizeof v, cudaMemcpyDeviceToHost));
+    CK(cudaMemset(h->d_wait_prof, 0, sizeof v));
+    for (int k = 0; k < 4; k++) ns_per_side[k] = v[k], waits_per_side[k] = v[4 + k];
+    return HEAT_OK;
+}
+
 extern "C" int heat_residual(heat_handle* h, float* residual)
 {
     if (!h || !residual) return fail(HEAT_E_INVALID, "heat_residual: bad arguments");
@@ -1058,6 +1100,11 @@ static int after_upload(heat_handle* h)
     // strip's ghost rows before the upload has landed
     h->seq++;
     const bool has[4] = {h->p.rank > 0, h->p.rank < h->p.nranks - 1, h->p.rank_y > 0, h->p.rank_y < h->p.nranks_y - 1};
+    if (h->gcol) { // the dense ghost-column arrays start as what the upload put into the field's ghost columns
+        heat_gather_ghost_columns<<<(h->nloc + 255) / 256, 256, 0, h->stream>>>(h->buf[0], h->buf[1], h->nloc, h->nyloc, h->pitch, h->gcol);
+        h->launches++;
+        CK(cudaGetLastError());
+    }
     if ((has[0] || has[1] || has[2] || has[3]) && h->connected && !h->external_halo) {
         if (h->local_nb[0] || h->local_nb[1] || h->local_nb[2] || h->local_nb[3]) {
             CK(cudaEventRecord(h->ev_done[h->seq & 1], h->stream));
@@ -1476,6 +1523,7 @@ static int open_side(heat_handle* h, int side, const void* blob)
     h->peer[side].buf[1] = (float*)((char*)base[1] + b.offset[1]);
     unsigned long long* f = (unsigned long long*)((char*)base[2] + b.offset[2]);
     h->peer[side].flag = &f[slot];
+    h->peer[side].gcol = (float*)((char*)f + GCOL_OFFSET);
     h->peer[side].nloc = b.nloc;
     h->peer[side].nyloc = b.nyloc;
     h->peer[side].pitch = b.pitch;
@@ -1536,6 +1584,7 @@ extern "C" int heat_connect_local2d(heat_handle* h, heat_handle* north, heat_han
         h->peer[side].buf[0] = o->buf[0];
         h->peer[side].buf[1] = o->buf[1];
         h->peer[side].flag = &o->flags[slot];
+        h->peer[side].gcol = o->gcol;
         h->peer[side].nloc = o->nloc;
         h->peer[side].nyloc = o->nyloc;
         h->peer[side].pitch = o->pitch;

@@ -20,6 +20,8 @@
 #define HEAT_ARITH_F32_NOFMA 1
 #define HEAT_ARITH_F64MIX 2
 
+#include <cuda/ptx>
+
 namespace heatk {
 
 // ------------------------------------------------------------------ arithmetic
@@ -48,6 +50,157 @@ __device__ __forceinline__ float upd(float c, float n, float s, float e, float w
         double t2 = __dsub_rn((double)__fadd_rn(e, w), c2);
         double r = __dadd_rn(__dadd_rn(cd, __dmul_rn((double)cx, t1)), __dmul_rn((double)cy, t2));
         return __double2float_rn(r);
+    }
+}
+
+// ---- MPI_F64MIX, four points at a time -------------------------------------------------------------
+// The scalar form above spends four conversions per point on the XU pipe (16 lanes/clk/SM): three
+// float->double widenings and the final narrowing; that pipe, not HBM, bounds the mode (ncu: XU 72 %).
+// Widening a NORMAL float is exact bit surgery -- sign kept, exponent re-biased by 896, mantissa
+// shifted up 29 bits -- which the integer pipes do at four times the XU rate.  Zero, denormals, inf and
+// nan do not fit that rule: ONE warp-uniform vote per float4 row decides whether every value to be
+// widened is normal; if any lane holds a special value the whole warp takes the conversion
+// instructions for that row.  HEAT_F64_WIDEN_INT = how many of the three widenings per point go the
+// integer way when the vote allows it (0 = none: the scalar form; 1 = the centre value; 2 = centre and
+// the N+S sum; 3 = all).  The final double->float rounding always stays a conversion instruction.
+#ifndef HEAT_F64_WIDEN_INT
+#define HEAT_F64_WIDEN_INT 0
+#endif
+
+__device__ __forceinline__ double widen_normal(float v)
+{
+    const unsigned b = __float_as_uint(v);
+    const unsigned hi = ((((b & 0x7fffffffu) >> 3) + 0x38000000u)) | (b & 0x80000000u);
+    return __hiloint2double((int)hi, (int)(b << 29));
+}
+// (bits << 1) - 2^24 is below 0xfe000000 exactly for normal numbers (biased exponent 1..254)
+__device__ __forceinline__ unsigned normal_key(float v) { return (__float_as_uint(v) << 1) - 0x01000000u; }
+
+template <int NINT>
+__device__ __forceinline__ float4 upd4_f64mix(const float4& c, const float4& n, const float4& s, float wl, float er, float cx,
+                                              float cy)
+{
+    const float cv[4] = {c.x, c.y, c.z, c.w};
+    const float sn[4] = {__fadd_rn(s.x, n.x), __fadd_rn(s.y, n.y), __fadd_rn(s.z, n.z), __fadd_rn(s.w, n.w)};
+    const float ew[4] = {__fadd_rn(c.y, wl), __fadd_rn(c.z, c.x), __fadd_rn(c.w, c.y), __fadd_rn(er, c.z)};
+    bool fast = false;
+    if (NINT > 0) {
+        unsigned k = 0;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            k = max(k, normal_key(cv[i]));
+            if (NINT > 1) k = max(k, normal_key(sn[i]));
+            if (NINT > 2) k = max(k, normal_key(ew[i]));
+        }
+        fast = __all_sync(0xffffffffu, k < 0xfe000000u);
+    }
+    const double dcx = (double)cx, dcy = (double)cy;
+    float o[4];
+    if (fast) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const double cd = widen_normal(cv[i]);
+            const double c2 = __dadd_rn(cd, cd);
+            const double t1 = __dsub_rn(NINT > 1 ? widen_normal(sn[i]) : (double)sn[i], c2);
+            const double t2 = __dsub_rn(NINT > 2 ? widen_normal(ew[i]) : (double)ew[i], c2);
+            o[i] = __double2float_rn(__dadd_rn(__dadd_rn(cd, __dmul_rn(dcx, t1)), __dmul_rn(dcy, t2)));
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const double cd = (double)cv[i];
+            const double c2 = __dadd_rn(cd, cd);
+            const double t1 = __dsub_rn((double)sn[i], c2);
+            const double t2 = __dsub_rn((double)ew[i], c2);
+            o[i] = __double2float_rn(__dadd_rn(__dadd_rn(cd, __dmul_rn(dcx, t1)), __dmul_rn(dcy, t2)));
+        }
+    }
+    return make_float4(o[0], o[1], o[2], o[3]);
+}
+
+// ---- float modes, four points at a time with the packed FP32 instructions of sm_100 ------------------
+// FADD2 / FMUL2 / FFMA2 do two IEEE-rounded float operations per instruction on the register pairs a float4
+// already sits in after LDG.128.  Same operations in the same order as upd<>, hence the same bits; only the
+// four E+W sums stay scalar (their operands straddle the pairs): 16 floating-point instructions per float4
+// instead of 28.  Build-time switch HEAT_PACKED_F32 (K1's plain path and K4's fast path).
+#ifndef HEAT_PACKED_F32
+#define HEAT_PACKED_F32 0
+#endif
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float a, float b)
+{
+    f32x2 r;
+    asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ void upk2(f32x2 r, float& a, float& b) { asm("mov.b64 {%0,%1}, %2;" : "=f"(a), "=f"(b) : "l"(r)); }
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c)
+{
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+
+template <int ARITH>
+__device__ __forceinline__ float4 upd4_packed(const float4& c, const float4& n, const float4& s, float wl, float er, float cx,
+                                              float cy)
+{
+    const f32x2 c01 = pk2(c.x, c.y), c23 = pk2(c.z, c.w);
+    const f32x2 cc01 = add2(c01, c01), cc23 = add2(c23, c23);
+    const f32x2 a01 = sub2(add2(pk2(s.x, s.y), pk2(n.x, n.y)), cc01);
+    const f32x2 a23 = sub2(add2(pk2(s.z, s.w), pk2(n.z, n.w)), cc23);
+    // E + W: (c.y + wl, c.z + c.x, c.w + c.y, er + c.z)
+    const f32x2 b01 = sub2(pk2(__fadd_rn(c.y, wl), __fadd_rn(c.z, c.x)), cc01);
+    const f32x2 b23 = sub2(pk2(__fadd_rn(c.w, c.y), __fadd_rn(er, c.z)), cc23);
+    const f32x2 cx2 = pk2(cx, cx), cy2 = pk2(cy, cy);
+    f32x2 o01, o23;
+    if constexpr (ARITH == HEAT_ARITH_F32_FMA) {
+        o01 = fma2(cy2, b01, fma2(cx2, a01, c01));
+        o23 = fma2(cy2, b23, fma2(cx2, a23, c23));
+    } else {
+        o01 = add2(add2(c01, mul2(cx2, a01)), mul2(cy2, b01));
+        o23 = add2(add2(c23, mul2(cx2, a23)), mul2(cy2, b23));
+    }
+    float4 o;
+    upk2(o01, o.x, o.y);
+    upk2(o23, o.z, o.w);
+    return o;
+}
+
+// One float4 of a row whose four columns are all interior, E/W neighbours across the float4 given (all lanes of
+// the warp must call this together: the MPI_F64MIX form votes).
+template <int ARITH>
+__device__ __forceinline__ float4 upd_quad(const float4& c, const float4& n, const float4& s, float wl, float er, float cx, float cy)
+{
+    if constexpr (ARITH == HEAT_ARITH_F64MIX && HEAT_F64_WIDEN_INT > 0) {
+        return upd4_f64mix<HEAT_F64_WIDEN_INT>(c, n, s, wl, er, cx, cy);
+    } else if constexpr (ARITH != HEAT_ARITH_F64MIX && HEAT_PACKED_F32) {
+        return upd4_packed<ARITH>(c, n, s, wl, er, cx, cy);
+    } else {
+        float4 o;
+        o.x = upd<ARITH>(c.x, n.x, s.x, c.y, wl, cx, cy);
+        o.y = upd<ARITH>(c.y, n.y, s.y, c.z, c.x, cx, cy);
+        o.z = upd<ARITH>(c.z, n.z, s.z, c.w, c.y, cx, cy);
+        o.w = upd<ARITH>(c.w, n.w, s.w, er, c.z, cx, cy);
+        return o;
     }
 }
 
@@ -163,13 +316,22 @@ struct strip_sync {
     unsigned count[4];                 // how many CTAs touch the neighbour on each side
     int* status;                       // raised when a wait times out
     unsigned long long timeout_ns;
+    unsigned long long* prof;          // diagnostics (HEAT_PROFILE_WAIT=1), else null: [0..3] ns the edge CTAs spent
+                                       // waiting per side, [4..7] number of waits per side
 };
 
-// Column neighbours of a 2-D block: where my first / last owned column goes (one float per row).
+// Column neighbours of a 2-D block.  Ghost columns do not travel into the neighbour's field: a store per row
+// into a column of a peer's field touches a new page of peer memory every row or two (the row pitch is tens of
+// kilobytes), and the address translation of those stores, not their bytes, is what limits the pass (two column
+// neighbours at 65536^2: 65536 stores per pass, 1.07 ms instead of 0.63).  Instead every block keeps, per buffer
+// and side, a DENSE array with one float per local row; a block stores its first / last owned column into the
+// neighbour's dense array of the new buffer and reads its own dense arrays of the old buffer in place of the
+// ghost column of its field (which is never written again after the upload).
 struct col_peers {
-    float* w;          // west neighbour's new buffer, element (local row 0, its last local column)
-    float* e;          // east neighbour's new buffer, element (local row 0, local column 0)
-    int64_t pitch_w, pitch_e;
+    float* w;          // west neighbour's dense EAST-ghost array (new buffer), indexed by local row
+    float* e;          // east neighbour's dense WEST-ghost array (new buffer)
+    const float* gw_in; // my dense WEST-ghost array of the buffer I read (values of local column 0)
+    const float* ge_in; // my dense EAST-ghost array of the buffer I read (values of local column ny-1)
     int edge_first;    // HEAT_COLS_FIRST = M > 0: column-edge CTAs are handed out before the rest of the block and
                        // each covers M tile rows (see cols_first); 0 = plain grid order
 };
@@ -205,7 +367,17 @@ __device__ __forceinline__ void strip_wait(const strip_sync& sy, bool edge_n, bo
         if (threadIdx.x == 0) {
 #pragma unroll
             for (int k = 0; k < 4; k++)
-                if (e[k]) spin_until(sy.wait[k], sy.wait_value, sy.timeout_ns, sy.status);
+                if (e[k]) {
+                    unsigned long long t0 = 0;
+                    if (sy.prof) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+                    spin_until(sy.wait[k], sy.wait_value, sy.timeout_ns, sy.status);
+                    if (sy.prof) {
+                        unsigned long long t1;
+                        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                        atomicAdd(&sy.prof[k], t1 - t0);
+                        atomicAdd(&sy.prof[4 + k], 1ull);
+                    }
+                }
         }
         __syncthreads();
     }
@@ -375,11 +547,7 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
                 float er = __shfl_down_sync(FULL, c.x, 1);
                 if (lane == 0) wl = ec;
                 if (lane == 31) er = ec;
-                float4 o;
-                o.x = upd<ARITH>(c.x, n.x, s[u].x, c.y, wl, cx, cy);
-                o.y = upd<ARITH>(c.y, n.y, s[u].y, c.z, c.x, cx, cy);
-                o.z = upd<ARITH>(c.z, n.z, s[u].z, c.w, c.y, cx, cy);
-                o.w = upd<ARITH>(c.w, n.w, s[u].w, er, c.z, cx, cy);
+                const float4 o = upd_quad<ARITH>(c, n, s[u], wl, er, cx, cy);
                 st4(q, o);
                 if (RESID) {
                     m = fmaxf(m, fabsf(__fsub_rn(c.x, o.x)));
@@ -408,6 +576,19 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
 #pragma unroll
         for (int u = 0; u < UNROLL; u++) {
             if (r + u < r1) {
+                if (COLS) {
+                    // the ghost columns of row r+u come from the dense arrays, not from the field
+                    if (cp.gw_in && col == 0) c.x = cp.gw_in[r + u];
+                    if (cp.ge_in) {
+                        const float g = (col <= ny - 1 && ny - 1 < col + 4) || (lane == 31 && col + 4 == ny - 1) ? cp.ge_in[r + u] : 0.0f;
+                        const int j = ny - 1 - col;
+                        if (j == 0) c.x = g;
+                        if (j == 1) c.y = g;
+                        if (j == 2) c.z = g;
+                        if (j == 3) c.w = g;
+                        if (lane == 31 && j == 4) ec = g;
+                    }
+                }
                 float wl = __shfl_up_sync(FULL, c.w, 1);
                 float er = __shfl_down_sync(FULL, c.x, 1);
                 if (lane == 0) wl = ec;
@@ -430,14 +611,14 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
                         if (!(ge && col + 2 == ny - 1)) q[2] = o.z;
                         if (!(ge && col + 3 == ny - 1)) q[3] = o.w;
                         // my first owned column (local column 1) is the west neighbour's ghost column
-                        if (gw && col == 0) cp.w[(int64_t)(r + u) * cp.pitch_w] = o.y;
+                        if (gw && col == 0) cp.w[r + u] = o.y;
                     } else {
                         st4(q, o);
                     }
                     // my last owned column (local column ny-2) is the east neighbour's ghost column
                     if (COLS && cp.e && col <= ny - 2 && ny - 2 < col + 4) {
                         const int j = ny - 2 - col;
-                        cp.e[(int64_t)(r + u) * cp.pitch_e] = j == 0 ? o.x : j == 1 ? o.y : j == 2 ? o.z : o.w;
+                        cp.e[r + u] = j == 0 ? o.x : j == 1 ? o.y : j == 2 ? o.z : o.w;
                     }
                     // K3: the first / last `ghost` updated rows are the neighbours' ghost rows
                     if (peer_n && r + u < row_lo + ghost) st4(peer_n + (int64_t)(r + u - row_lo) * pitch + col, o);
@@ -462,6 +643,75 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
     if (SYNC) strip_signal(sy, edge_n, edge_s, edge_w, edge_e);
 }
 
+// ------------------------------------------------------------------ K1b: the same update from a shared-memory tile
+// The alternative north_star names: a tile with its halo rows is staged in shared memory by the bulk-copy
+// engine (cp.async.bulk, one copy per row, completion on an mbarrier), then every thread computes its float4
+// column of the tile from shared memory.  One tile per CTA, no pipelining inside the CTA: the other CTAs of the
+// SM (21 KB of shared memory each) cover the copy latency.  HEAT_K1_VARIANT=bulk, single strip, no residual.
+// It moves exactly the bytes K1 moves and adds an LDS per LDG, so it is here to be MEASURED against K1.
+template <int ARITH, int ROWS, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+heat_step_bulk(const float* __restrict__ in, float* __restrict__ out, int row_lo, int row_hi, int ny, int64_t pitch, float cx,
+               float cy, int reverse, int* __restrict__ status)
+{
+    namespace ptx = cuda::ptx;
+    constexpr int W = THREADS * 4, HALO = 4, SW = W + 2 * HALO; // staged row: 4 columns of halo on either side
+    __shared__ __align__(128) float tile[(ROWS + 2) * SW];
+    __shared__ __align__(8) uint64_t bar;
+    const int npitch = (int)pitch, tid = threadIdx.x;
+    const int ntiles = gridDim.y;
+    const int t = reverse ? ntiles - 1 - (int)blockIdx.y : (int)blockIdx.y;
+    const int r0 = row_lo + t * ROWS, r1 = min(r0 + ROWS, row_hi), nrows = r1 - r0;
+    const int col0 = blockIdx.x * W;
+    // staged columns [c_lo, c_hi) of rows r0-1 .. r1; column c sits at tile[row * SW + (c - (col0 - HALO))]
+    const int c_lo = max(col0 - HALO, 0), c_hi = min(col0 + W + HALO, npitch);
+    const unsigned row_bytes = (unsigned)(c_hi - c_lo) * 4u; // a multiple of 16: every bound is a multiple of 4 floats
+    if (tid == 0) {
+        ptx::mbarrier_init(&bar, 1);
+        ptx::fence_proxy_async(ptx::space_shared); // the barrier's initialisation must be visible to the copy engine
+    }
+    __syncthreads();
+    if (tid == 0) {
+        ptx::mbarrier_arrive_expect_tx(ptx::sem_release, ptx::scope_cta, ptx::space_shared, &bar, row_bytes * (unsigned)(nrows + 2));
+        for (int i = 0; i < nrows + 2; i++)
+            ptx::cp_async_bulk(ptx::space_cluster, ptx::space_global, tile + i * SW + (c_lo - (col0 - HALO)),
+                               in + (int64_t)(r0 - 1 + i) * pitch + c_lo, row_bytes, &bar);
+    }
+    // bounded wait: a mismatch between expected and copied bytes must end in a wrong answer, not in a hang
+    unsigned tries = 0;
+    while (!ptx::mbarrier_try_wait_parity(&bar, 0u)) {
+        if (++tries > (1u << 22)) {
+            if (tid == 0) *status = 2;
+            break;
+        }
+    }
+    const int col = col0 + tid * 4;
+    if (col >= npitch) return;
+    const bool kx = (col == 0) || (col >= ny - 1), ky = (col + 1 >= ny - 1), kz = (col + 2 >= ny - 1), kw = (col + 3 >= ny - 1);
+    const float* c_row = tile + SW + HALO + tid * 4; // row r0, my first column
+    float4 n = *reinterpret_cast<const float4*>(c_row - SW);
+    float4 c = *reinterpret_cast<const float4*>(c_row);
+    float* q = out + (int64_t)r0 * pitch + col;
+    for (int i = 0; i < nrows; i++) {
+        const float4 s = *reinterpret_cast<const float4*>(c_row + SW);
+        const float wl = c_row[-1], er = c_row[4]; // garbage only where the result is a ring / padding column
+        float4 o;
+        o.x = upd<ARITH>(c.x, n.x, s.x, c.y, wl, cx, cy);
+        o.y = upd<ARITH>(c.y, n.y, s.y, c.z, c.x, cx, cy);
+        o.z = upd<ARITH>(c.z, n.z, s.z, c.w, c.y, cx, cy);
+        o.w = upd<ARITH>(c.w, n.w, s.w, er, c.z, cx, cy);
+        if (kx) o.x = c.x;
+        if (ky) o.y = c.y;
+        if (kz) o.z = c.z;
+        if (kw) o.w = c.w;
+        st4(q, o);
+        n = c;
+        c = s;
+        c_row += SW;
+        q += pitch;
+    }
+}
+
 // ------------------------------------------------------------------ K4 temporal blocking
 // T updates per pass over HBM, bit-identical to T single updates.  Pure register pipeline, no
 // shared memory, no block barrier: a warp owns 128 consecutive columns (one float4 per lane) and
@@ -481,12 +731,7 @@ __device__ __forceinline__ float4 upd4(const float4& c, const float4& n, const f
 {
     const float wl = __shfl_up_sync(0xffffffffu, c.w, 1);
     const float er = __shfl_down_sync(0xffffffffu, c.x, 1);
-    float4 o;
-    o.x = upd<ARITH>(c.x, n.x, s.x, c.y, wl, cx, cy);
-    o.y = upd<ARITH>(c.y, n.y, s.y, c.z, c.x, cx, cy);
-    o.z = upd<ARITH>(c.z, n.z, s.z, c.w, c.y, cx, cy);
-    o.w = upd<ARITH>(c.w, n.w, s.w, er, c.z, cx, cy);
-    return o;
+    return upd_quad<ARITH>(c, n, s, wl, er, cx, cy);
 }
 
 // Fast path of K4 for a warp whose 128 columns hold no ring/padding column and whose tile is far
@@ -837,6 +1082,19 @@ heat_absdiff_max(const float* __restrict__ a, const float* __restrict__ b, int r
         }
     }
     block_max_to_global(m, resid);
+}
+
+// 2-D blocks: after an upload both buffers hold the ghost columns in the field; copy them into the dense
+// arrays the update kernel reads (gcol layout: [buffer][side: 0 west, 1 east][local row]).
+__global__ void heat_gather_ghost_columns(const float* __restrict__ b0, const float* __restrict__ b1, int nloc, int ny,
+                                          int64_t pitch, float* __restrict__ gcol)
+{
+    for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < nloc; r += gridDim.x * blockDim.x) {
+        gcol[0 * (int64_t)nloc + r] = b0[(int64_t)r * pitch];
+        gcol[1 * (int64_t)nloc + r] = b0[(int64_t)r * pitch + ny - 1];
+        gcol[2 * (int64_t)nloc + r] = b1[(int64_t)r * pitch];
+        gcol[3 * (int64_t)nloc + r] = b1[(int64_t)r * pitch + ny - 1];
+    }
 }
 
 // ------------------------------------------------------------------ strip flags

@@ -55,13 +55,13 @@ class _CudaRows:
 
 
 class StripSolver:
-    """The solver loop of one strip; every rank of the process group makes one.
+    """The solver loop of one strip; every rank of the process group makes one."""
 
-    solver_cls / rows_cls exist so that the CPU test (gloo, world_size 2) can drive this
-    very class with an oracle-backed stand-in; the product always uses the defaults.
-    """
+    # what computes a strip and what exposes single rows of it to torch.distributed: the CUDA library
+    make_solver = staticmethod(api.HeatSolver)
+    make_rows = staticmethod(_CudaRows)
 
-    def __init__(self, nx, ny, *, group=None, device=None, halo="p2p", cols=1, solver_cls=None, rows_cls=None, **params):
+    def __init__(self, nx, ny, *, group=None, device=None, halo="p2p", cols=1, **params):
         """cols > 1: 2-D blocks, world = (world // cols) row blocks x cols column blocks (the reference's
         cartesian topology, M:51-75); rank r is block (r // cols, r % cols).  halo='p2p' only."""
         import torch.distributed as dist
@@ -82,23 +82,22 @@ class StripSolver:
             raise ValueError("2-D blocks move their ghost columns with peer stores only (halo='p2p')")
         self.cols, self.gx = cols, self.world // cols
         self.bx, self.by = divmod(self.rank, cols)
-        cls = solver_cls or api.HeatSolver
         if cols > 1:
             params = dict(params, rank_y=self.by, nranks_y=cols)
-        self.solver = cls(nx, ny, rank=self.bx, nranks=self.gx, device=device, **params)
+        self.solver = self.make_solver(nx, ny, rank=self.bx, nranks=self.gx, device=device, **params)
         self.row0, self.rows = api.strip_rows(nx, self.gx, self.bx)
         self.col0, self.ncols = api.strip_rows(ny, cols, self.by)
         self.lo, self.hi = local_window(nx, self.gx, self.bx)
         self.nloc = self.hi - self.lo
         self.conv_every = int(self.solver.params.conv_every)
-        self._rows = (rows_cls or _CudaRows)(self.solver)
+        self._rows = self.make_rows(self.solver)
         if self.halo == "p2p":
             self._connect_p2p()
         elif self.halo == "sendrecv":
             if int(self.solver.params.temporal_block) > 1:
                 raise ValueError("halo='sendrecv' moves one ghost row per update: use temporal_block=1 (or halo='p2p')")
             self.solver.set_halo_mode(api.HALO_EXTERNAL)
-            if solver_cls is None:
+            if self.dist.get_backend(self.group) == "nccl":
                 # NCCL P2P ops are ordered against torch's current stream: run the updates there too
                 import torch
                 self.solver.set_stream(torch.cuda.current_stream(device).cuda_stream)

@@ -92,7 +92,11 @@ def _worker(rank, world, port, shape, steps, params, out_path):
         from oracle import pyoracle as O
         from parallel_heat_b200.strips import StripSolver
         u = O.inidat(*shape)
-        s = StripSolver(shape[0], shape[1], halo="sendrecv", solver_cls=OracleStrip, rows_cls=NumpyRows, **params)
+
+        class CpuStrips(StripSolver):  # same host logic, strips computed by the oracle (no GPU here)
+            make_solver = staticmethod(OracleStrip)
+            make_rows = staticmethod(NumpyRows)
+        s = CpuStrips(shape[0], shape[1], halo="sendrecv", **params)
         s.upload(u)
         done, conv = s.run(steps)
         full = s.gather(0)
