@@ -282,9 +282,7 @@ def run_reference_arm(args, wl, rank, world):
         return
     cores = host_cores()
     glups, updates, secs, kind, sample, note, (rnx, rny), used = reference_sample(wl, cores, 20.0, args.steps + max(args.warmup, 3))
-    cfg = config_of(wl, "MPI_F64MIX", 1, "none", 1)
-    if (rnx, rny) != (wl["nx"], wl["ny"]):
-        cfg["nx"], cfg["ny"] = rnx, rny
+    cfg = config_of(dict(wl, nx=rnx, ny=rny), "MPI_F64MIX", 1, "none", 1)  # the grid that was really timed
     out = {"metric": METRIC, "value": glups, "unit": "GLUP/s", "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": secs / updates * 1e3, "higher_is_better": True, "scaling": wl["scaling"],
            "vs_baseline": None, "dtype": "f32 grid, f64-mixed arithmetic (M:168-174)", "data": "synthetic", "config": cfg,
@@ -500,7 +498,7 @@ def run_one(ctx, api, wl, arith, args):
         achieved = BYTES_PER_LUP * own_lups / (kernel_ms * 1e-3) / 1e9
         kname = "heat_step_tb" if T > 1 else "heat_step_vec"
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": ncu_traffic(f"{kname}@{wl['name']}") or ncu_traffic(kname), "kernel": kname, "peak_source": peak_src,
+                    "traffic": ncu_traffic(f"{kname}@{nx}x{ny}"), "kernel": kname, "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": BYTES_PER_LUP * own_lups,
                     "note": "8 B per point-update x interior points of this GPU's strip / (median repetition / launches per repetition)"
                             + (" (effective: temporal blocking re-uses tiles on chip)" if T > 1 else "")}

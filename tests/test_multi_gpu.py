@@ -134,3 +134,26 @@ def test_blocks_one_process_per_gpu(tmp_path, oracle, ph, shape, steps, params):
                                       conv_every=params.get("conv_every", 0), conv_phase=params.get("conv_phase", 1))
     assert (int(r["done"]), bool(r["conv"])) == (wdone, wconv)
     assert np.array_equal(r["full"].view(np.uint32), want.view(np.uint32))
+
+
+@needs2
+@pytest.mark.timeout(900)
+@pytest.mark.parametrize("cols,shape,steps,params", [
+    # many passes across processes (hundreds of flag epochs in both sweep directions): row strips, then 2-D blocks
+    # with both kinds of neighbours (cols = world on 2 GPUs: column neighbours only; on 4 and 8 GPUs: 2x2, 2x4)
+    (1, (1030, 2052), 600, dict(arith=0)),
+    (1, (1030, 2052), 600, dict(arith=2, temporal_block=4)),
+    (0, (1100, 4100), 500, dict(arith=0)),
+    (0, (1100, 4100), 500, dict(arith=1, cols_first=4)),
+])
+def test_long_runs_across_processes(tmp_path, oracle, ph, cols, shape, steps, params):
+    import torch.multiprocessing as mp
+    world = 8 if ngpus() >= 8 else 4 if ngpus() >= 4 else 2
+    if cols == 0:
+        cols = world // 2 if world >= 4 else 2
+    out = tmp_path / "out.npz"
+    mp.spawn(_worker, args=(world, _free_port(), shape, steps, "p2p", dict(params), str(out), cols), nprocs=world, join=True)
+    r = np.load(out)
+    want, wdone, _ = oracle.solve(oracle.inidat(*shape), steps, arith=params.get("arith", 0))
+    assert int(r["done"]) == wdone
+    assert np.array_equal(r["full"].view(np.uint32), want.view(np.uint32))
