@@ -1,7 +1,7 @@
 #!/bin/bash
 # round 2, two GPUs: the cross-process tests the 1-GPU lease skips, then the driver's bench command at N=2
 mkdir -p gpurun_out
-timeout 1200 python -m pytest tests/test_multi_gpu.py -x -q -m gpu > gpurun_out/pytest_multi.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_multi.log
+timeout 1500 python -m pytest tests/ -x -q -m gpu > gpurun_out/pytest_multi.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_multi.log
 tail -n 5 gpurun_out/pytest_multi.log
 TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1 --nproc-per-node 2"
 : > gpurun_out/n2.log
