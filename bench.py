@@ -58,6 +58,9 @@ def workload(name, n):
     if name == "weak32k":
         return dict(name=name, nx=32768 * n, ny=32768, conv_every=0, temporal_block=4, scaling="weak",
                     text=f"{32768 * n}x32768 float32 inidat field, {n} strip(s), 4 updates per HBM pass")
+    if name == "g16k":
+        return dict(name=name, nx=16384, ny=16384, conv_every=0, temporal_block=1, scaling="weak",
+                    text="16384x16384 float32 inidat field, no convergence check (A/B runs of kernel variants)")
     if name == "c1":
         return dict(name=name, nx=1024, ny=1024, conv_every=0, temporal_block=1, scaling="weak", text="1024x1024 float32 inidat field")
     raise SystemExit(f"unknown workload {name}")
@@ -158,12 +161,25 @@ class ClockSampler:
     def nvlink_kib(self):
         """(tx, rx) KiB moved over all NVLinks of this GPU so far (NVML field values), or None."""
         nv = self.nv
-        try:
-            v = nv.nvmlDeviceGetFieldValues(self.h, [(nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, 0xFFFFFFFF),
-                                                     (nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX, 0xFFFFFFFF)])
-            if v[0].nvmlReturn != 0 or v[1].nvmlReturn != 0:
-                return None
-            return int(v[0].value.ullVal), int(v[1].value.ullVal)
+        if nv is None:
+            return None
+        ids = (nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX)
+        try:  # scope UINT_MAX = the sum over the links
+            v = nv.nvmlDeviceGetFieldValues(self.h, [(ids[0], 0xFFFFFFFF), (ids[1], 0xFFFFFFFF)])
+            if v[0].nvmlReturn == 0 and v[1].nvmlReturn == 0:
+                return int(v[0].value.ullVal), int(v[1].value.ullVal)
+        except Exception:
+            pass
+        try:  # else link by link
+            tot = [0, 0]
+            seen = False
+            for link in range(18):
+                v = nv.nvmlDeviceGetFieldValues(self.h, [(ids[0], link), (ids[1], link)])
+                for k in range(2):
+                    if v[k].nvmlReturn == 0:
+                        tot[k] += int(v[k].value.ullVal)
+                        seen = True
+            return tuple(tot) if seen else None
         except Exception:
             return None
 
@@ -609,46 +625,45 @@ def e2e_single(ctx, api, wl, arith, K):
 
 
 def e2e_strips(ctx, api, wl, arith, args):
-    """Strips: every rank brings its own window of the field in pinned host memory, uploads it, runs K updates and
-    reads its rows back; wall clock between barriers (max over ranks by construction)."""
+    """N GPUs, field in HOST memory: every rank holds the rows of its strip plus K more on either side (pinned),
+    and calls heat_solve() on that window -- H2D, K updates and D2H overlapped band by band, no exchange with the
+    neighbours (the K outer rows are recomputed on both sides of a cut instead; strips.solve_strip_on_host_rows).
+    Wall clock between barriers, so the slowest rank counts."""
+    import numpy as np
     torch, dist = ctx.torch, ctx.dist
-    from parallel_heat_b200.strips import StripSolver
+    from parallel_heat_b200 import strips
     nx, ny, T = wl["nx"], wl["ny"], wl["temporal_block"]
     K = max(args.steps // T, 1) * T
-    s = StripSolver(nx, ny, device=ctx.local_rank, halo=args.halo, cols=1, arith=arith, conv_every=0, temporal_block=T)
-    try:
-        solver = s.solver
-        if args.halo == "p2p":
-            solver.set_stream(ctx.stream.cuda_stream)
-        s.init_inidat()
-        _, _, nloc, lo = solver.device_view(0)
-        host = torch.empty((nloc, ny), dtype=torch.float32, pin_memory=True)
-        host.numpy()[...] = inidat_window(nx, ny, lo, lo + nloc, 0, ny)
-        back = torch.empty((s.rows, ny), dtype=torch.float32, pin_memory=True)
-        secs = []
-        for k in range(3):  # first round = warm-up
-            ctx.barrier()
-            t0 = time.perf_counter()
-            solver.upload_local(host.numpy())
-            dist.barrier()  # nobody stores into a neighbour whose upload has not landed (flags order it; belt and braces)
-            s.enqueue(K)
-            s.sync()
-            solver.download_local(back.numpy())
-            ctx.barrier()
-            if k > 0:
-                secs.append(time.perf_counter() - t0)
-        dt = sorted(secs)[len(secs) // 2]
-        tot = torch.tensor([float(nloc * ny * 4), float(s.rows * ny * 4), dt], device="cuda", dtype=torch.float64)
-        mx = tot.clone()
-        dist.all_reduce(tot)
-        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        dt = float(mx[2].item())
-        return {"value": (nx - 2) * (ny - 2) * K / dt / 1e9, "unit": "GLUP/s",
-                "h2d_bytes_per_step": float(tot[0].item()) / K, "d2h_bytes_per_step": float(tot[1].item()) / K,
-                "call": f"per rank: heat_upload_local (pinned host window) + {K} updates + heat_download_local, "
-                        "wall clock between barriers, median of 2 rounds after one warm-up round, max over ranks", "seconds": dt}
-    finally:
-        s.close()
+    lo, hi = strips.overlap_window(nx, ctx.world, ctx.rank, K)
+    row0, rows = api.strip_rows(nx, ctx.world, ctx.rank)
+    host = torch.empty((hi - lo, ny), dtype=torch.float32, pin_memory=True)
+    hn = host.numpy()
+    secs, own = [], None
+    for k in range(3):  # first round = warm-up
+        hn[...] = inidat_window(nx, ny, lo, hi, 0, ny)
+        ctx.barrier()
+        t0 = time.perf_counter()
+        own, done = strips.solve_strip_on_host_rows(hn, nx, ctx.world, ctx.rank, K, device=ctx.local_rank, arith=arith,
+                                                    temporal_block=T)
+        ctx.barrier()
+        if k > 0:
+            secs.append(time.perf_counter() - t0)
+    nw, npts, nbad = parity_windows(ctx, wl, arith, (row0, rows, 0, ny), K,
+                                    lambda r0, r1, c0, c1: np.ascontiguousarray(own[r0 - row0:r1 - row0, c0:c1]))
+    dt = sorted(secs)[len(secs) // 2]
+    tot = torch.tensor([float((hi - lo) * ny * 4), float((hi - lo) * ny * 4), float(nw), float(npts), float(nbad)], device="cuda",
+                       dtype=torch.float64)
+    mx = torch.tensor([dt], device="cuda", dtype=torch.float64)
+    dist.all_reduce(tot)
+    dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    dt = float(mx.item())
+    tot = tot.tolist()
+    return {"value": (nx - 2) * (ny - 2) * K / dt / 1e9, "unit": "GLUP/s",
+            "h2d_bytes_per_step": tot[0] / K, "d2h_bytes_per_step": tot[1] / K,
+            "call": f"per rank: heat_solve(steps={K}) on its pinned host window = own rows + {K} rows either side (no halo exchange: "
+                    "the overlap is recomputed), H2D + updates + D2H overlapped band by band; wall clock between barriers, "
+                    "median of 2 rounds after one warm-up round, max over ranks", "seconds": dt,
+            "parity": {"windows": int(tot[2]), "points": int(tot[3]), "mismatches": int(tot[4]), "bit_exact": tot[4] == 0, "updates": K}}
 
 
 def run_ours(args, wl, rank, world, local_rank):
@@ -711,6 +726,15 @@ def run_ours(args, wl, rank, world, local_rank):
                 if wl["name"] != "c2":
                     leg("mpi_f64mix_c2_8192", "c2", api.MPI_F64MIX, "8192x8192 in the MPI program's arithmetic")
             also["reference_cuda"] = reference_cuda_leg(peak)
+
+        if world > 1 and not args.no_also and args.cols == 1 and wl["name"] != "weak32k":
+            # BASELINE configs[4] on the same N GPUs: weak scaling, 32768^2 per GPU, 4 updates per HBM pass
+            w = workload("weak32k", world)
+            r = run_one(ctx, api, w, arith, args)
+            r.update(workload=w["text"], arith=api.ARITH_NAMES[arith], scaling="weak", effective_gbs=r["value"] * BYTES_PER_LUP,
+                     effective_frac_per_gpu=r["value"] * BYTES_PER_LUP / peak / world,
+                     note="weak scaling of configs[4]: compare with also.weak32k_T4 of the 1-GPU line")
+            also = {"weak32k_T4": r}
 
         base = None
         if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -35,6 +35,36 @@ def local_window(nx, nranks, rank):
     return lo, hi
 
 
+def overlap_window(nx, nranks, rank, depth):
+    """Global rows [lo, hi) from which strip `rank` can compute its own rows for `depth` updates on its own:
+    its rows plus `depth` more on either side (clipped to the grid).  After k updates only the k outermost
+    rows of such a window are wrong (its first and last row are treated as a fixed ring), so after `depth`
+    updates every owned row is exact -- redundant work of 2*depth rows instead of any exchange."""
+    r0, n = api.strip_rows(nx, nranks, rank)
+    return max(0, r0 - depth), min(nx, r0 + n + depth)
+
+
+def solve_strip_on_host_rows(window_rows, nx, nranks, rank, steps, **params):
+    """One-shot solve of ONE strip from host memory, without communication: heat_solve() on the overlap window
+    (window_rows: float32 array holding global rows overlap_window(nx, nranks, rank, updates), all ny columns;
+    overwritten).  For few updates on a field that lives in host memory the PCIe copies are the cost, and this
+    keeps every GPU's H2D, updates and D2H overlapped (heat_solve streams its window in bands) with no step that
+    waits for a neighbour; the strips of the reference exchange a halo per update instead (M:160-177).
+    Returns (view of the rows this strip owns, updates_done).  Convergence checks need the exchanging path."""
+    import ctypes as C
+    if params.get("conv_every", 0):
+        raise ValueError("solve_strip_on_host_rows: no convergence check (use StripSolver.run)")
+    updates = steps + (1 if params.get("step_convention", api.STEPS_CUDA) == api.STEPS_MPI else 0)
+    lo, hi = overlap_window(nx, nranks, rank, updates)
+    r0, n = api.strip_rows(nx, nranks, rank)
+    if window_rows.shape[0] != hi - lo or window_rows.dtype != np.float32 or not window_rows.flags.c_contiguous:
+        raise ValueError(f"window must be C-contiguous float32 with rows [{lo}, {hi})")
+    p = api.default_params(nx=hi - lo, ny=window_rows.shape[1], steps=steps, **params)
+    done, conv = C.c_int(0), C.c_int(0)
+    api._check(api.load().heat_solve(C.byref(p), window_rows.ctypes.data_as(C.POINTER(C.c_float)), C.byref(done), C.byref(conv)))
+    return window_rows[r0 - lo:r0 - lo + n], done.value
+
+
 class _CudaRows:
     """torch views of single rows of a strip's device buffer (for halo='sendrecv')."""
 

@@ -321,6 +321,24 @@ def test_streamed_solve_8192(ph, oracle):
         assert_same_bits(got[r0:r0 + band], want[r0 - lo:r0 - lo + band], f"8192^2 streamed rows {r0}..")
 
 
+@pytest.mark.parametrize("T", [1, 4])
+def test_strips_from_host_rows_without_exchange(ph, oracle, T):
+    # every strip solved on its own from host rows + `updates` rows of overlap (strips.solve_strip_on_host_rows):
+    # the assembled field is the undecomposed one, bit for bit; strips shorter than the overlap included
+    from parallel_heat_b200 import strips
+    for (nx, ny), g, steps in [((640, 300), 4, 12), ((1000, 517), 3, 20), ((300, 200), 5, 40)]:
+        u = field((nx, ny), seed=nx + g)
+        want, _, _ = oracle.solve(u, steps, arith=1)
+        got = u.copy()
+        for r in range(g):
+            lo, hi = strips.overlap_window(nx, g, r, steps)
+            own, done = strips.solve_strip_on_host_rows(np.ascontiguousarray(u[lo:hi]), nx, g, r, steps, arith=1, temporal_block=T)
+            r0, n = ph.strip_rows(nx, g, r)
+            assert done == steps and own.shape == (n, ny)
+            got[r0:r0 + n] = own
+        assert_same_bits(got, want, f"{g} strips from host rows, {steps} updates, T={T}")
+
+
 # ---------------------------------------------------------------- K4: temporal blocking
 @pytest.mark.parametrize("T", [2, 4])
 @pytest.mark.parametrize("arith", MODES)

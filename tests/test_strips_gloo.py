@@ -138,3 +138,13 @@ def test_partition_and_windows(ph):
     assert strips.local_window(10, 3, 1) == (3, 8)
     assert strips.local_window(10, 3, 2) == (6, 10)
     assert strips.local_window(10, 1, 0) == (0, 10)
+
+
+def test_overlap_windows(ph):
+    from parallel_heat_b200 import strips
+    # own rows + depth on either side, clipped to the grid
+    assert strips.overlap_window(100, 4, 0, 10) == (0, 35)
+    assert strips.overlap_window(100, 4, 1, 10) == (15, 60)
+    assert strips.overlap_window(100, 4, 3, 10) == (65, 100)
+    assert strips.overlap_window(100, 4, 1, 1000) == (0, 100)
+    assert strips.overlap_window(100, 1, 0, 7) == (0, 100)
