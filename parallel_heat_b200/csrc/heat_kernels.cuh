@@ -1065,6 +1065,154 @@ __global__ void __launch_bounds__(1024, 1) heat_resident(resident_args a)
     }
 }
 
+// ------------------------------------------------------------------ double-precision grids
+// The reference hard-codes `float` (M:46, C:170); this is its update with the element type widened: every value
+// and every operation in double, cx/cy the float constants promoted (struct Parms stays float, M:29-32).
+// FMA = true contracts the two multiply-adds like nvcc does for the CUDA source, false rounds every operation
+// like gcc does for the MPI source.  16 B per point-update, so the HBM roofline is half the float one in LUP/s.
+// Same structure as K1/K2/K3: lanes along iy, each thread owns 2 consecutive columns (one 16-byte access), N/C/S
+// rows in registers, E/W by shuffle, first/last `ghost` rows also stored into the neighbour strips, step flags
+// fused in.  Ring columns are written back unchanged, ring rows never written.
+template <bool FMA>
+__device__ __forceinline__ double upd64(double c, double n, double s, double e, double w, double cx, double cy)
+{
+    const double t1 = __dsub_rn(__dadd_rn(s, n), __dadd_rn(c, c));
+    const double t2 = __dsub_rn(__dadd_rn(e, w), __dadd_rn(c, c));
+    if (FMA) return __fma_rn(cy, t2, __fma_rn(cx, t1, c));
+    return __dadd_rn(__dadd_rn(c, __dmul_rn(cx, t1)), __dmul_rn(cy, t2));
+}
+
+__global__ void heat_inidat_f64_kernel(double* __restrict__ a, double* __restrict__ b, int nx, int ny, int row_lo, int nloc,
+                                       int64_t pitch, int col_lo, int nyloc)
+{
+    const int64_t total = (int64_t)nloc * pitch;
+    for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
+        const int lr = (int)(k / pitch);
+        const int ly = (int)(k - (int64_t)lr * pitch);
+        const int ix = row_lo + lr, iy = col_lo + ly;
+        double v = 0.0;
+        if (ly < nyloc) {
+            uint32_t p = (uint32_t)ix * (uint32_t)(nx - ix - 1) * (uint32_t)iy * (uint32_t)(ny - iy - 1);
+            v = (double)(int32_t)p; // the int product wraps before the conversion, whatever the element type (M:320)
+        }
+        a[k] = v;
+        b[k] = v;
+    }
+}
+
+__device__ __forceinline__ void block_max_to_global64(double m, unsigned long long* gmax)
+{
+    // non-negative doubles order like their bit patterns
+    unsigned long long bits = (unsigned long long)__double_as_longlong(m);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, bits, o);
+        bits = other > bits ? other : bits;
+    }
+    __shared__ unsigned long long smax64[32];
+    const int warp = threadIdx.x >> 5, nwarp = (blockDim.x + 31) >> 5;
+    if ((threadIdx.x & 31) == 0) smax64[warp] = bits;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long v = 0;
+        for (int w = 0; w < nwarp; w++) v = smax64[w] > v ? smax64[w] : v;
+        if (v != 0ull) atomicMax(gmax, v);
+    }
+}
+
+template <bool FMA, bool RESID, bool SYNC>
+__global__ void __launch_bounds__(128, 8)
+heat_step_f64(const double* __restrict__ in, double* __restrict__ out, int row_lo, int row_hi, int ny, int64_t pitch,
+              int rows_per_tile, double cx, double cy, unsigned long long* __restrict__ resid, double* peer_n, double* peer_s,
+              int ghost, int reverse, strip_sync sy)
+{
+    constexpr int UNROLL = 4;
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int npitch = (int)pitch;
+    int col = ((int)blockIdx.x * 128 + threadIdx.x) * 2;
+    const int ntiles = gridDim.y;
+    const int tile = tile_of_block<SYNC>((int)blockIdx.y, ntiles, reverse);
+    const int r0 = row_lo + tile * rows_per_tile;
+    const int r1 = min(r0 + rows_per_tile, row_hi);
+    const bool edge_n = r0 < row_lo + ghost, edge_s = r1 > row_hi - ghost;
+    if (SYNC) strip_wait(sy, edge_n, edge_s);
+
+    double m = 0.0;
+    const bool live = col < npitch;
+    if (col - lane * 2 < npitch) { // else the whole warp is beyond the row (warp-uniform)
+        if (!live) col = npitch - 2; // keep the lane in bounds for loads; it never stores
+        const bool kx = (col == 0) || (col >= ny - 1), ky = (col + 1 >= ny - 1); // ring / padding columns: copied through
+        const bool edge_lane = (lane == 0 && col > 0) || (lane == 31 && col + 2 < npitch);
+        const int edge_off = (lane == 0) ? -1 : 2;
+        const double* p = in + (int64_t)(r0 - 1) * pitch + col;
+        double* q = out + (int64_t)r0 * pitch + col;
+        double2 n = *reinterpret_cast<const double2*>(p);
+        double2 c = *reinterpret_cast<const double2*>(p + pitch);
+        double ec = edge_lane ? p[pitch + edge_off] : 0.0;
+        p += 2 * pitch;
+        for (int r = r0; r < r1; r += UNROLL) {
+            double2 s[UNROLL];
+            double es[UNROLL];
+#pragma unroll
+            for (int u = 0; u < UNROLL; u++) {
+                const int64_t off = (int64_t)min(u, r1 - 1 - r) * pitch; // rows past the tile: clamped, loaded, unused
+                s[u] = *reinterpret_cast<const double2*>(p + off);
+                es[u] = edge_lane ? p[off + edge_off] : 0.0;
+            }
+#pragma unroll
+            for (int u = 0; u < UNROLL; u++) {
+                if (r + u < r1) {
+                    double wl = __shfl_up_sync(FULL, c.y, 1);
+                    double er = __shfl_down_sync(FULL, c.x, 1);
+                    if (lane == 0) wl = ec;
+                    if (lane == 31) er = ec;
+                    double2 o;
+                    o.x = upd64<FMA>(c.x, n.x, s[u].x, c.y, wl, cx, cy);
+                    o.y = upd64<FMA>(c.y, n.y, s[u].y, er, c.x, cx, cy);
+                    if (kx) o.x = c.x;
+                    if (ky) o.y = c.y;
+                    if (live) {
+                        *reinterpret_cast<double2*>(q) = o;
+                        if (peer_n && r + u < row_lo + ghost)
+                            *reinterpret_cast<double2*>(peer_n + (int64_t)(r + u - row_lo) * pitch + col) = o;
+                        if (peer_s && r + u >= row_hi - ghost)
+                            *reinterpret_cast<double2*>(peer_s + (int64_t)(r + u - (row_hi - ghost)) * pitch + col) = o;
+                    }
+                    if (RESID) {
+                        m = fmax(m, fabs(__dsub_rn(c.x, o.x)));
+                        m = fmax(m, fabs(__dsub_rn(c.y, o.y)));
+                    }
+                    n = c;
+                    c = s[u];
+                    ec = es[u];
+                    q += pitch;
+                }
+            }
+            p += (int64_t)UNROLL * pitch;
+        }
+    }
+    if (RESID) block_max_to_global64(live ? m : 0.0, resid);
+    if (SYNC) strip_signal(sy, edge_n, edge_s);
+}
+
+__global__ void __launch_bounds__(256)
+heat_absdiff_max_f64(const double* __restrict__ a, const double* __restrict__ b, int row_lo, int row_hi, int ny, int64_t pitch,
+                     unsigned long long* __restrict__ resid)
+{
+    double m = 0.0;
+    const int64_t total = (int64_t)(row_hi - row_lo) * pitch;
+    for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
+        const int lr = (int)(k / pitch);
+        const int iy = (int)(k - (int64_t)lr * pitch);
+        if (iy < ny) {
+            const int64_t idx = k + (int64_t)row_lo * pitch;
+            m = fmax(m, fabs(__dsub_rn(a[idx], b[idx])));
+        }
+    }
+    block_max_to_global64(m, resid);
+}
+
 // ------------------------------------------------------------------ residual of two buffers
 // max |a-b| over the interior of a strip (heat_residual(): a separate pass, not on the hot path)
 __global__ void __launch_bounds__(256)
