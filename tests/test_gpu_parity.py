@@ -332,7 +332,7 @@ def test_strips_from_host_rows_without_exchange(ph, oracle, T):
         got = u.copy()
         for r in range(g):
             lo, hi = strips.overlap_window(nx, g, r, steps)
-            own, done = strips.solve_strip_on_host_rows(np.ascontiguousarray(u[lo:hi]), nx, g, r, steps, arith=1, temporal_block=T)
+            own, done = strips.solve_strip_on_host_rows(u[lo:hi].copy(), nx, g, r, steps, arith=1, temporal_block=T)  # solved in place
             r0, n = ph.strip_rows(nx, g, r)
             assert done == steps and own.shape == (n, ny)
             got[r0:r0 + n] = own
