@@ -257,7 +257,7 @@ struct heat_handle {
     heat_handle* local_nb[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev_done[2] = {nullptr, nullptr}; // recorded after epoch e in ev_done[e & 1]
     bool serpentine = true;
-    bool k1_bulk = false; // HEAT_K1_VARIANT=bulk: the shared-memory staged variant of K1 (for measurements)
+    int k1_variant = 2; // HEAT_K1_VARIANT: 0 = vec (register streaming), 1 = bulk (shared-memory staged), 2 = auto (bulk for long rows)
     int cols_first = 0; // HEAT_COLS_FIRST = M: column-edge CTAs ahead of the rest, M tile rows each (2-D blocks across processes)
     // CUDA graphs of GRAPH_PASSES consecutive passes, one per (newest buffer, sweep direction, fused?)
     cudaGraphExec_t graphs[2][2][2] = {};
@@ -437,7 +437,10 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     h->serpentine = env_int("HEAT_SERPENTINE", 1) != 0;
     {
         const char* v = getenv("HEAT_K1_VARIANT");
-        h->k1_bulk = v && !strcmp(v, "bulk");
+        h->k1_variant = !v || !*v || !strcmp(v, "auto") ? 2 : !strcmp(v, "bulk") ? 1 : 0;
+#ifdef HEAT_BOUNDS_CHECK
+        h->k1_variant = 0; // the checked build watches the loads of the register-streaming kernels
+#endif
     }
     h->cols_first = env_int("HEAT_COLS_FIRST", 0);
     if (h->cols_first < 0) h->cols_first = 0;
@@ -490,6 +493,11 @@ static void count_edge_ctas(heat_handle* h, int rows, int rpt, unsigned grid_x, 
     h->sync_args.count[2] = h->sync_args.count[3] = tiles; // one west-edge and one east-edge CTA per tile row
 }
 
+#ifndef HEAT_BULK_ROWS
+#define HEAT_BULK_ROWS 8 // tile height of the shared-memory staged kernel
+#endif
+static const int64_t BULK_MIN_PITCH = 16384; // floats per row from which "auto" stages tiles in shared memory
+
 template <int ARITH, bool RESID>
 static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, float* peer_n, float* peer_s, int reverse)
 {
@@ -504,6 +512,27 @@ static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, fl
     if ((rows + rpt - 1) / rpt > 65535) rpt = (rows + 65534) / 65535; // grid.y limit: taller tiles
     dim3 grid((unsigned)((h->pitch / 4 + THREADS - 1) / THREADS), (unsigned)((rows + rpt - 1) / rpt));
     count_edge_ctas(h, rows, rpt, grid.x, grid.y);
+    // K1b, the shared-memory staged variant: measured faster than the register-streaming kernel where rows are long
+    // (16384 floats and more), slower below; "auto" picks by row length.  Row strips and the residual are supported,
+    // column blocks are not.
+    const bool bulk = h->p.nranks_y == 1 && (h->k1_variant == 1 || (h->k1_variant == 2 && h->pitch >= BULK_MIN_PITCH));
+    if (bulk) {
+        constexpr int ROWS = HEAT_BULK_ROWS;
+        if (h->ghost <= ROWS && (rows + ROWS - 1) / ROWS <= 65535) {
+            dim3 g((unsigned)((h->pitch / 4 + THREADS - 1) / THREADS), (unsigned)((rows + ROWS - 1) / ROWS));
+            count_edge_ctas(h, rows, ROWS, g.x, g.y);
+            if (h->sync_args.counters)
+                heat_step_bulk<ARITH, RESID, ROWS, THREADS, true><<<g, THREADS, 0, h->stream>>>(
+                    in, out, h->upd_lo, h->upd_hi, ny, h->pitch, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse,
+                    h->sync_args, h->d_status);
+            else
+                heat_step_bulk<ARITH, RESID, ROWS, THREADS, false><<<g, THREADS, 0, h->stream>>>(
+                    in, out, h->upd_lo, h->upd_hi, ny, h->pitch, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse,
+                    h->sync_args, h->d_status);
+            h->launches++;
+            return cudaGetLastError();
+        }
+    }
     if (h->p.nranks_y > 1) { // 2-D blocks: column neighbours too
         const int M = h->col_args.edge_first, xe = ((ny - 2) >> 2) / THREADS;
         if (M > 1 && h->sync_args.counters && cols_first_active((int)grid.x, (int)grid.y, xe))
@@ -521,12 +550,7 @@ static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, fl
         heat_step_vec<ARITH, RESID, THREADS, UNROLL, true><<<grid, THREADS, 0, h->stream>>>(
             in, out, h->upd_lo, h->upd_hi, ny, h->pitch, rpt, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse,
             h->sync_args);
-    else if (!RESID && h->k1_bulk && !peer_n && !peer_s) {
-        constexpr int ROWS = 8;
-        dim3 g((unsigned)((h->pitch / 4 + THREADS - 1) / THREADS), (unsigned)((rows + ROWS - 1) / ROWS));
-        heat_step_bulk<ARITH, ROWS, THREADS><<<g, THREADS, 0, h->stream>>>(in, out, h->upd_lo, h->upd_hi, ny, h->pitch, h->p.cx, h->p.cy,
-                                                                          reverse, h->d_status);
-    } else
+    else
         heat_step_vec<ARITH, RESID, THREADS, UNROLL, false><<<grid, THREADS, 0, h->stream>>>(
             in, out, h->upd_lo, h->upd_hi, ny, h->pitch, rpt, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse,
             h->sync_args);
