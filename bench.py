@@ -61,6 +61,9 @@ def workload(name, n):
     if name == "g16k":
         return dict(name=name, nx=16384, ny=16384, conv_every=0, temporal_block=1, scaling="weak",
                     text="16384x16384 float32 inidat field, no convergence check (A/B runs of kernel variants)")
+    if name == "g16k_f64":
+        return dict(name=name, nx=16384, ny=16384, conv_every=0, temporal_block=1, scaling="weak", f64=True,
+                    text="16384x16384 DOUBLE-precision inidat field (HEAT_GRID_F64; 16 B per point-update), no convergence check")
     if name == "c1":
         return dict(name=name, nx=1024, ny=1024, conv_every=0, temporal_block=1, scaling="weak", text="1024x1024 float32 inidat field")
     raise SystemExit(f"unknown workload {name}")
@@ -405,13 +408,13 @@ def measure(ctx, enqueue, sync, K, W, reps=None, launch_count=lambda: 0, before_
             "host_secs": t1 - t0, "launches": n1 - n0, "extra": extra}
 
 
-def device_window(torch, ptr, pitch, r0, r1, c0, c1, device):
-    """Rows [r0, r1) x columns [c0, c1) of a strip's local device array, as numpy."""
+def device_window(torch, ptr, pitch, r0, r1, c0, c1, device, es=4):
+    """Rows [r0, r1) x columns [c0, c1) of a strip's local device array (pitch in elements of es bytes), as numpy."""
     class _Arr:
         pass
     a = _Arr()
-    a.__cuda_array_interface__ = {"shape": (r1 - r0, c1 - c0), "strides": (4 * pitch, 4), "typestr": "<f4", "version": 3,
-                                  "data": (ptr + 4 * (pitch * r0 + c0), False)}
+    a.__cuda_array_interface__ = {"shape": (r1 - r0, c1 - c0), "strides": (es * pitch, es), "typestr": f"<f{es}", "version": 3,
+                                  "data": (ptr + es * (pitch * r0 + c0), False)}
     return torch.as_tensor(a, device=f"cuda:{device}").cpu().numpy()
 
 
@@ -446,10 +449,15 @@ def parity_windows(ctx, wl, arith, view, updates, get):
     for (r0, r1) in sorted(rows):
         for (c0, c1) in sorted(cols):
             R0, R1, C0, C1 = max(0, r0 - U), min(nx, r1 + U), max(0, c0 - U), min(ny, c1 + U)
-            want, _, _ = O.solve(inidat_window(nx, ny, R0, R1, C0, C1), U, arith=arith)
+            ini = inidat_window(nx, ny, R0, R1, C0, C1)
+            if wl.get("f64"):  # double grids: the oracle's double mode (parity unpinned, see oracle/heat_oracle.c)
+                want, _, _ = O.solve_f64(ini.astype(np.float64), U, fused=(arith == 0))
+            else:
+                want, _, _ = O.solve(ini, U, arith=arith)
             want = want[r0 - R0:r1 - R0, c0 - C0:c1 - C0]
             got = get(r0, r1, c0, c1)
-            n_bad += int((got.view(np.uint32) != want.view(np.uint32)).sum())
+            bits = np.uint64 if wl.get("f64") else np.uint32
+            n_bad += int((got.view(bits) != want.view(bits)).sum())
             n_win += 1
             n_pts += got.size
     return n_win, n_pts, n_bad
@@ -461,6 +469,11 @@ def run_one(ctx, api, wl, arith, args):
     nx, ny = wl["nx"], wl["ny"]
     T = wl["temporal_block"]
     params = dict(arith=arith, conv_every=wl["conv_every"], temporal_block=T)
+    es = 4
+    if wl.get("f64"):
+        params["grid_type"] = api.GRID_F64
+        es = 8
+    bytes_per_lup = BYTES_PER_LUP * es / 4
     s = None
     if args.k3_profile:
         os.environ["HEAT_PROFILE_WAIT"] = "1"  # read by heat_create: the edge CTAs time their flag waits
@@ -511,12 +524,12 @@ def run_one(ctx, api, wl, arith, args):
         step_launches = K // T
         own_lups = (min(rows_own, nx - 2) if world > 1 else nx - 2) * min(cols_own, ny - 2) * T
         kernel_ms = ms / max(step_launches, 1)
-        achieved = BYTES_PER_LUP * own_lups / (kernel_ms * 1e-3) / 1e9
-        kname = "heat_step_tb" if T > 1 else "heat_step_vec"
+        achieved = bytes_per_lup * own_lups / (kernel_ms * 1e-3) / 1e9
+        kname = "heat_step_tb" if T > 1 else "heat_step_f64" if es == 8 else "heat_step_vec"
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                     "traffic": ncu_traffic(f"{kname}@{nx}x{ny}"), "kernel": kname, "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": BYTES_PER_LUP * own_lups,
-                    "note": "8 B per point-update x interior points of this GPU's strip / (median repetition / launches per repetition)"
+                    "algorithmic_bytes_per_launch": bytes_per_lup * own_lups,
+                    "note": f"{bytes_per_lup:.0f} B per point-update x interior points of this GPU's strip / (median repetition / launches per repetition)"
                             + (" (effective: temporal blocking re-uses tiles on chip)" if T > 1 else "")}
 
         # parity of this very code path (same solver object, same kernels, same neighbours), outside the timed region
@@ -530,7 +543,7 @@ def run_one(ctx, api, wl, arith, args):
             ptr, pitch, nloc, lo = solver.device_view(0)
 
             def get(r0, r1, c0, c1):
-                return device_window(torch, ptr, pitch, r0 - lo, r1 - lo, c0 - lo_c, c1 - lo_c, ctx.local_rank)
+                return device_window(torch, ptr, pitch, r0 - lo, r1 - lo, c0 - lo_c, c1 - lo_c, ctx.local_rank, es)
             # 2-D blocks keep their ghost COLUMNS in dense side arrays, not in the field: owned columns only there
             vc0, vc1 = (s.col0, s.col0 + s.ncols) if (world > 1 and args.cols > 1) else (lo_c, hi_c)
             nw, npts, nbad = parity_windows(ctx, wl, arith, (lo, nloc, vc0, vc1 - vc0), U, get)
@@ -725,6 +738,8 @@ def run_ours(args, wl, rank, world, local_rank):
                     "arithmetic (M:168-174): bit-identical to what the --impl reference arm computes")
                 if wl["name"] != "c2":
                     leg("mpi_f64mix_c2_8192", "c2", api.MPI_F64MIX, "8192x8192 in the MPI program's arithmetic")
+            leg("f64_grid_16384", "g16k_f64", arith, "SURVEY 8(f) rank 4: the same update on a DOUBLE-precision grid (16 B per point-update, "
+                "so the HBM roofline is half as many LUP/s); parity unpinned -- the reference has no double build")
             also["reference_cuda"] = reference_cuda_leg(peak)
 
         if world > 1 and not args.no_also and args.cols == 1 and wl["name"] != "weak32k":

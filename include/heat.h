@@ -38,6 +38,14 @@ extern "C" {
 #define HEAT_F32_NOFMA   1 /* C:155-161 with -fmad=false: float, every op rounded         */
 #define HEAT_MPI_F64MIX  2 /* M:168-174: float neighbour sums, rest in double (2.0 literal) */
 
+/* Element type of the grid.  The reference hard-codes float; HEAT_GRID_F64 is its update with `double u`
+ * (SURVEY 8(f) rank 4): all values and operations in double, cx/cy still the float constants promoted.
+ * With a double grid `arith` only chooses the contraction: HEAT_F32_FMA = two fused multiply-adds, as nvcc builds
+ * the CUDA source; the other two = every operation rounded, as gcc builds the MPI source.  Single updates on
+ * one strip or row strips (temporal_block 1, nranks_y 1); data moves through the *_f64 entry points. */
+#define HEAT_GRID_F32    0
+#define HEAT_GRID_F64    1
+
 /* How many updates `steps` means, and when convergence is checked. */
 #define HEAT_STEPS_CUDA  0 /* `steps` updates                 (C:204  i <  STEPS) */
 #define HEAT_STEPS_MPI   1 /* `steps`+1 updates               (M:159  it <= STEPS) */
@@ -59,6 +67,7 @@ typedef struct heat_params {
     int   device;          /* CUDA device ordinal of this strip                        */
     int   rank, nranks;    /* row-strip decomposition: this handle owns strip `rank`   */
     int   rank_y, nranks_y;/* column blocks on top of that (2-D blocks, M:51-75); 0, 1 = row strips only */
+    int   grid_type;       /* HEAT_GRID_F32 (the reference's `float u`, M:46, C:170) | HEAT_GRID_F64       */
 } heat_params;
 
 typedef struct heat_handle heat_handle; /* opaque: owns device buffers, stream, graphs */
@@ -82,6 +91,7 @@ int heat_device_count(void);
 /* ---- the reference's helpers, same arguments (M:315-341, C:274-300) ------------------ */
 /* inidat: u[ix*ny+iy] = (float)(ix*(nx-ix-1)*iy*(ny-iy-1)) in wrapping int32 (M:320). */
 int heat_inidat(int nx, int ny, float *u);
+int heat_inidat_f64(int nx, int ny, double *u); /* same int product, same wrap, stored as double */
 /* prtdat: "%6.1f" text, iy descending outer, ix ascending inner (M:326-341). */
 int heat_prtdat(int nx, int ny, const float *u, const char *fnam);
 /* Binary twin of prtdat: 16-byte header {"HEATB200", int32 nx, int32 ny} + nx*ny floats. */
@@ -98,6 +108,8 @@ int heat_readdat_bin(const char *fnam, int *nx, int *ny, float *u, size_t capaci
  * memory (cudaHostAlloc / cudaHostRegister) to get that overlap; pageable memory works but copies
  * synchronously.  HEAT_SOLVE_STREAMED=0 switches the overlap off, HEAT_SOLVE_BAND_ROWS sets the band. */
 int heat_solve(const heat_params *p, float *grid, int *updates_done, int *converged);
+/* The same for a double-precision grid (p->grid_type = HEAT_GRID_F64). */
+int heat_solve_f64(const heat_params *p, double *grid, int *updates_done, int *converged);
 
 /* The same over the first `ngpus` devices of this process: one row strip per GPU, ghost rows moved by
  * peer stores over NVLink, one host thread.  Replaces M:51-297 (topology, scatter, halo requests, loop,
@@ -120,6 +132,7 @@ int heat_set_stream(heat_handle *h, void *cuda_stream);
  * neighbours have finished the pass this strip finished last, so that none of their ghost-row stores
  * can land on top of the new field. */
 int heat_upload(heat_handle *h, const float *full_grid);
+int heat_upload_f64(heat_handle *h, const double *full_grid);   /* handles created with HEAT_GRID_F64 */
 /* Same from a device pointer holding the full field (used when the field is already in HBM). */
 int heat_upload_device(heat_handle *h, const void *d_full_grid);
 /* inidat evaluated on the device straight into both buffers (bit-identical to heat_inidat). */
@@ -142,6 +155,7 @@ int heat_residual(heat_handle *h, float *residual);
 /* Newest field -> host; a strip writes only the rows (a 2-D block: rows x columns) it owns into
  * full_grid, so every rank of a job may download into the same array. */
 int heat_download(heat_handle *h, float *full_grid);
+int heat_download_f64(heat_handle *h, double *full_grid);
 /* The same for a rank that holds only its strip: local_rows = the strip's window, dense
  * local_rows x ny (global rows first_global_row ..., ghost rows included: see heat_device_view);
  * own_rows receives the rows the strip owns (heat_strip_rows), dense.  Row strips only:

@@ -145,3 +145,74 @@ int oracle_solve(int arith, int nx, int ny, int steps, float cx, float cy,
     if (converged) *converged = conv;
     return 0;
 }
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Double-precision grids.  PARITY UNPINNED: the reference hard-codes `float u` (M:46,
+ * C:170), so there is no reference build or golden vector for this mode; it is the reference's expression
+ * (M:168-174 / C:155-161) restated with `double u` -- every value and operation in double, parms.cx/cy still
+ * floats (M:29-32) promoted.  fused = 0: every operation rounded (what gcc makes of the MPI source);
+ * fused = 1: the two multiply-adds contracted, as nvcc does for the CUDA source. */
+void oracle_inidat_f64(int nx, int ny, double *u)
+{
+    for (int ix = 0; ix < nx; ix++) {
+        uint32_t a = (uint32_t)ix * (uint32_t)(nx - ix - 1);
+        for (int iy = 0; iy < ny; iy++)
+            u[(int64_t)ix * ny + iy] = (double)(int32_t)(a * (uint32_t)iy * (uint32_t)(ny - iy - 1)); /* int product, M:320 */
+    }
+}
+
+void oracle_step_f64(int fused, int nx, int ny, float cxf, float cyf, const double *in, double *out)
+{
+    const double cx = (double)cxf, cy = (double)cyf;
+#pragma omp parallel for schedule(static)
+    for (int i = 1; i < nx - 1; i++) {
+        const double *c = in + (int64_t)i * ny, *n = c - ny, *s = c + ny;
+        double *o = out + (int64_t)i * ny;
+        for (int j = 1; j < ny - 1; j++) {
+            const double t1 = (s[j] + n[j]) - 2.0 * c[j];
+            const double t2 = (c[j + 1] + c[j - 1]) - 2.0 * c[j];
+            if (fused) {
+                o[j] = fma(cy, t2, fma(cx, t1, c[j]));
+            } else {
+                const double a = cx * t1;
+                const double r = c[j] + a;
+                const double b = cy * t2;
+                o[j] = r + b;
+            }
+        }
+    }
+}
+
+int oracle_solve_f64(int fused, int nx, int ny, int steps, float cx, float cy, int conv_every, float conv_eps, int conv_phase,
+                     int step_convention, double *grid, double *work, int *updates_done, int *converged)
+{
+    if (nx < 1 || ny < 1 || steps < 0 || !grid || !work) return -1;
+    const int64_t n = (int64_t)nx * ny;
+    memcpy(work, grid, (size_t)n * sizeof(double));
+    double *buf[2] = {grid, work};
+    int old = 0, done = 0, conv = 0;
+    const int total = steps + (step_convention ? 1 : 0);
+    for (int it = 0; it < total; it++) {
+        oracle_step_f64(fused, nx, ny, cx, cy, buf[old], buf[1 - old]);
+        old = 1 - old;
+        done = it + 1;
+        if (conv_every > 0) {
+            int check = conv_phase ? (it % conv_every == 0) : ((it + 1) % conv_every == 0);
+            if (check) {
+                double m = 0.0;
+                for (int64_t k = 0; k < n; k++) {
+                    double d = fabs(buf[0][k] - buf[1][k]);
+                    if (d > m) m = d;
+                }
+                if (m < (double)conv_eps) {
+                    conv = 1;
+                    break;
+                }
+            }
+        }
+    }
+    if (old == 1) memcpy(grid, work, (size_t)n * sizeof(double));
+    if (updates_done) *updates_done = done;
+    if (converged) *converged = conv;
+    return 0;
+}

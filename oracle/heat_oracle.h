@@ -53,6 +53,13 @@ int oracle_solve(int arith, int nx, int ny, int steps, float cx, float cy,
                  int conv_every, float conv_eps, int conv_phase, int step_convention,
                  float *grid, float *work, int *updates_done, int *converged);
 
+/* Double-precision grids: PARITY UNPINNED (the reference has no double build; see heat_oracle.c).
+ * fused: 0 = every operation rounded, 1 = the two multiply-adds contracted. */
+void oracle_inidat_f64(int nx, int ny, double *u);
+void oracle_step_f64(int fused, int nx, int ny, float cx, float cy, const double *in, double *out);
+int oracle_solve_f64(int fused, int nx, int ny, int steps, float cx, float cy, int conv_every, float conv_eps,
+                     int conv_phase, int step_convention, double *grid, double *work, int *updates_done, int *converged);
+
 /* number of OpenMP threads the oracle will use (1 when built without OpenMP) */
 int oracle_threads(void);
 

@@ -50,6 +50,12 @@ def lib():
                                                    _fp, _fp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.oracle_solve.restype = C.c_int
         L.oracle_threads.restype = C.c_int
+        _dp = C.POINTER(C.c_double)
+        L.oracle_inidat_f64.argtypes = [C.c_int, C.c_int, _dp]
+        L.oracle_inidat_f64.restype = None
+        L.oracle_solve_f64.argtypes = [C.c_int] * 4 + [C.c_float, C.c_float, C.c_int, C.c_float, C.c_int, C.c_int,
+                                                       _dp, _dp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.oracle_solve_f64.restype = C.c_int
         _lib = L
     return _lib
 
@@ -101,6 +107,27 @@ def solve(grid, steps, arith=F32_NOFMA, cx=0.1, cy=0.1, conv_every=0, conv_eps=1
 
 def threads():
     return lib().oracle_threads()
+
+
+# double-precision grids: PARITY UNPINNED (no reference build exists for them, see heat_oracle.c)
+def inidat_f64(nx, ny):
+    u = np.empty((nx, ny), np.float64)
+    lib().oracle_inidat_f64(nx, ny, u.ctypes.data_as(C.POINTER(C.c_double)))
+    return u
+
+
+def solve_f64(grid, steps, fused=False, cx=0.1, cy=0.1, conv_every=0, conv_eps=1e-3, conv_phase=0, step_convention=0):
+    """Returns (final grid, updates_done, converged) for a float64 grid."""
+    g = np.array(grid, np.float64, order="C", copy=True)
+    nx, ny = g.shape
+    work = np.empty_like(g)
+    done, conv = C.c_int(0), C.c_int(0)
+    dp = C.POINTER(C.c_double)
+    rc = lib().oracle_solve_f64(int(bool(fused)), nx, ny, steps, cx, cy, conv_every, np.float32(conv_eps), conv_phase,
+                                step_convention, g.ctypes.data_as(dp), work.ctypes.data_as(dp), C.byref(done), C.byref(conv))
+    if rc:
+        raise ValueError("oracle_solve_f64: bad arguments")
+    return g, done.value, bool(conv.value)
 
 
 # ----------------------------------------------------------------------------

@@ -26,6 +26,7 @@ STEPS_CUDA, STEPS_MPI = 0, 1
 PHASE_MPI, PHASE_CUDA = 0, 1
 IPC_BLOB_BYTES = 256
 HALO_P2P, HALO_EXTERNAL = 0, 1
+GRID_F32, GRID_F64 = 0, 1
 
 
 class HeatError(RuntimeError):
@@ -39,12 +40,14 @@ class HeatParams(C.Structure):
     _fields_ = [("nx", C.c_int), ("ny", C.c_int), ("steps", C.c_int), ("cx", C.c_float), ("cy", C.c_float),
                 ("conv_every", C.c_int), ("conv_eps", C.c_float), ("conv_phase", C.c_int),
                 ("step_convention", C.c_int), ("arith", C.c_int), ("temporal_block", C.c_int),
-                ("device", C.c_int), ("rank", C.c_int), ("nranks", C.c_int), ("rank_y", C.c_int), ("nranks_y", C.c_int)]
+                ("device", C.c_int), ("rank", C.c_int), ("nranks", C.c_int), ("rank_y", C.c_int), ("nranks_y", C.c_int),
+                ("grid_type", C.c_int)]
 
 
 ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.POINTER(C.c_float), C.c_void_p)
 
 _fp = C.POINTER(C.c_float)
+_dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int)
 _H = C.c_void_p
 
@@ -58,6 +61,10 @@ SIGNATURES = {
     "heat_prtdat_bin": (C.c_int, [C.c_int, C.c_int, _fp, C.c_char_p]),
     "heat_readdat_bin": (C.c_int, [C.c_char_p, _ip, _ip, _fp, C.c_size_t]),
     "heat_solve": (C.c_int, [C.POINTER(HeatParams), _fp, _ip, _ip]),
+    "heat_solve_f64": (C.c_int, [C.POINTER(HeatParams), _dp, _ip, _ip]),
+    "heat_inidat_f64": (C.c_int, [C.c_int, C.c_int, _dp]),
+    "heat_upload_f64": (C.c_int, [_H, _dp]),
+    "heat_download_f64": (C.c_int, [_H, _dp]),
     "heat_solve_gpus": (C.c_int, [C.POINTER(HeatParams), C.c_int, _fp, _ip, _ip]),
     "heat_create": (C.c_int, [C.POINTER(HeatParams), C.POINTER(_H)]),
     "heat_destroy": (C.c_int, [_H]),
@@ -143,6 +150,12 @@ def inidat(nx, ny):
     return u
 
 
+def inidat_f64(nx, ny):
+    u = np.empty((nx, ny), np.float64)
+    _check(load().heat_inidat_f64(nx, ny, u.ctypes.data_as(_dp)))
+    return u
+
+
 def prtdat(u, fnam):
     u, p = _f32(u)
     _check(load().heat_prtdat(u.shape[0], u.shape[1], p, str(fnam).encode()))
@@ -168,11 +181,16 @@ def strip_rows(nx, nranks, rank):
 
 
 def solve(grid, steps, **params):
-    """One-shot heat_solve(): host grid in, newest field out.  Returns (field, updates_done, converged)."""
-    g = np.array(grid, dtype=np.float32, order="C", copy=True)
+    """One-shot heat_solve(): host grid in, newest field out.  Returns (field, updates_done, converged).
+    grid_type=GRID_F64 takes / returns float64 through heat_solve_f64()."""
+    f64 = params.get("grid_type", GRID_F32) == GRID_F64
+    g = np.array(grid, dtype=np.float64 if f64 else np.float32, order="C", copy=True)
     p = default_params(nx=g.shape[0], ny=g.shape[1], steps=steps, **params)
     done, conv = C.c_int(0), C.c_int(0)
-    _check(load().heat_solve(C.byref(p), g.ctypes.data_as(_fp), C.byref(done), C.byref(conv)))
+    if f64:
+        _check(load().heat_solve_f64(C.byref(p), g.ctypes.data_as(_dp), C.byref(done), C.byref(conv)))
+    else:
+        _check(load().heat_solve(C.byref(p), g.ctypes.data_as(_fp), C.byref(done), C.byref(conv)))
     return g, done.value, bool(conv.value)
 
 
@@ -217,10 +235,16 @@ class HeatSolver:
         _check(load().heat_set_stream(self._h, C.c_void_p(cuda_stream_ptr)))
 
     def upload(self, full_grid):
-        g, p = _f32(full_grid)
+        if self.params.grid_type == GRID_F64:
+            g = np.ascontiguousarray(full_grid, dtype=np.float64)
+        else:
+            g, p = _f32(full_grid)
         if g.shape != (self.params.nx, self.params.ny):
             raise ValueError(f"grid shape {g.shape} != ({self.params.nx}, {self.params.ny})")
-        _check(load().heat_upload(self._h, p))
+        if self.params.grid_type == GRID_F64:
+            _check(load().heat_upload_f64(self._h, g.ctypes.data_as(_dp)))
+        else:
+            _check(load().heat_upload(self._h, p))
 
     def upload_device(self, device_ptr):
         _check(load().heat_upload_device(self._h, C.c_void_p(device_ptr)))
@@ -229,10 +253,14 @@ class HeatSolver:
         _check(load().heat_init_inidat(self._h))
 
     def download(self, out=None):
+        f64 = self.params.grid_type == GRID_F64
         if out is None:
-            out = np.zeros((self.params.nx, self.params.ny), np.float32)
-        assert out.dtype == np.float32 and out.flags.c_contiguous
-        _check(load().heat_download(self._h, out.ctypes.data_as(_fp)))
+            out = np.zeros((self.params.nx, self.params.ny), np.float64 if f64 else np.float32)
+        assert out.dtype == (np.float64 if f64 else np.float32) and out.flags.c_contiguous
+        if f64:
+            _check(load().heat_download_f64(self._h, out.ctypes.data_as(_dp)))
+        else:
+            _check(load().heat_download(self._h, out.ctypes.data_as(_fp)))
         return out
 
     def upload_local(self, local_rows):

@@ -65,6 +65,7 @@ extern "C" int heat_params_default(heat_params* p)
     p->nranks = 1;
     p->rank_y = 0;
     p->nranks_y = 1;
+    p->grid_type = HEAT_GRID_F32;
     return HEAT_OK;
 }
 
@@ -76,6 +77,17 @@ extern "C" int heat_inidat(int nx, int ny, float* u)
         const uint32_t a = (uint32_t)ix * (uint32_t)(nx - ix - 1);
         float* row = u + (size_t)ix * ny;
         for (int iy = 0; iy < ny; iy++) row[iy] = (float)(int32_t)(a * (uint32_t)iy * (uint32_t)(ny - iy - 1));
+    }
+    return HEAT_OK;
+}
+
+extern "C" int heat_inidat_f64(int nx, int ny, double* u)
+{
+    if (nx < 1 || ny < 1 || !u) return fail(HEAT_E_INVALID, "heat_inidat_f64: bad arguments");
+    for (int ix = 0; ix < nx; ix++) {
+        const uint32_t a = (uint32_t)ix * (uint32_t)(nx - ix - 1);
+        double* row = u + (size_t)ix * ny;
+        for (int iy = 0; iy < ny; iy++) row[iy] = (double)(int32_t)(a * (uint32_t)iy * (uint32_t)(ny - iy - 1));
     }
     return HEAT_OK;
 }
@@ -209,13 +221,14 @@ struct heat_handle {
     int upd_lo = 1, upd_hi = 0; // local rows [upd_lo, upd_hi) are the ones this strip updates
     int col0 = 0, cols_own = 0; // owned global columns [col0, col0+cols_own) (2-D blocks; else all)
     int lo_c = 0, nyloc = 0;    // local array = global columns [lo_c, lo_c+nyloc): + one ghost column per neighbour
-    int64_t pitch = 0;          // floats
+    int64_t pitch = 0;          // row pitch in FLOATS (4-byte units) whatever the element type: buf[k] + r*pitch is row r
+    int es = 1;                 // floats per element: 1 = float grid, 2 = double grid (HEAT_GRID_F64)
     float* buf[2] = {nullptr, nullptr};
     int cur = 0;                // index of the newest buffer
     cudaStream_t stream = nullptr;
     bool own_stream = false;
-    unsigned* d_resid = nullptr;
-    unsigned* h_resid = nullptr; // pinned
+    unsigned* d_resid = nullptr; // max|old-new| as bits: 4 bytes used for float grids, 8 for double grids
+    unsigned* h_resid = nullptr; // pinned, 8 bytes
     int* d_status = nullptr;     // mapped pinned: wait-kernel time-outs
     int* h_status = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_resid = nullptr;
@@ -244,7 +257,7 @@ struct heat_handle {
     heat_handle* local_nb[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev_done[2] = {nullptr, nullptr}; // recorded after epoch e in ev_done[e & 1]
     bool serpentine = true;
-    bool k1_bulk = false; // HEAT_K1_VARIANT=bulk: the shared-memory staged variant of K1 (for measurements)
+    int k1_variant = 2; // HEAT_K1_VARIANT: 0 = vec (register streaming), 1 = bulk (shared-memory staged), 2 = auto (bulk for long rows)
     int cols_first = 0; // HEAT_COLS_FIRST = M: column-edge CTAs ahead of the rest, M tile rows each (2-D blocks across processes)
     // CUDA graphs of GRAPH_PASSES consecutive passes, one per (newest buffer, sweep direction, fused?)
     cudaGraphExec_t graphs[2][2][2] = {};
@@ -297,6 +310,9 @@ static int validate(const heat_params* p)
         return fail(HEAT_E_INVALID, "params: rank_y=%d nranks_y=%d", p->rank_y, p->nranks_y);
     if (p->nranks_y > 1 && (p->ny / p->nranks_y < 2 || p->temporal_block != 1))
         return fail(HEAT_E_INVALID, "params: column blocks need >= 2 columns each and temporal_block 1");
+    if (p->grid_type != HEAT_GRID_F32 && p->grid_type != HEAT_GRID_F64) return fail(HEAT_E_INVALID, "params: grid_type=%d", p->grid_type);
+    if (p->grid_type == HEAT_GRID_F64 && (p->temporal_block != 1 || p->nranks_y != 1))
+        return fail(HEAT_E_INVALID, "params: double-precision grids run single updates on row strips (temporal_block 1, nranks_y 1)");
     if (p->conv_phase != HEAT_PHASE_MPI && p->conv_phase != HEAT_PHASE_CUDA)
         return fail(HEAT_E_INVALID, "params: conv_phase=%d", p->conv_phase);
     if (p->step_convention != HEAT_STEPS_CUDA && p->step_convention != HEAT_STEPS_MPI)
@@ -367,8 +383,9 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     h->lo_c = (p->rank_y > 0) ? h->col0 - 1 : 0;
     const int hi_c = (p->rank_y < p->nranks_y - 1) ? h->col0 + h->cols_own + 1 : p->ny;
     h->nyloc = hi_c - h->lo_c;
-    // rows padded to 128 bytes so that every row starts on a float4 (and a cache line)
-    h->pitch = ((int64_t)h->nyloc + 31) / 32 * 32;
+    // rows padded to 128 bytes so that every row starts on a float4 / double2 (and a cache line)
+    h->es = p->grid_type == HEAT_GRID_F64 ? 2 : 1;
+    h->pitch = ((int64_t)h->nyloc * h->es + 31) / 32 * 32;
 
     const size_t bytes = (size_t)h->nloc * h->pitch * sizeof(float);
 #define CKH(call)                                                                                      \
@@ -386,9 +403,9 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     const size_t flag_bytes = GCOL_OFFSET + (p->nranks_y > 1 ? 4 * (size_t)h->nloc * sizeof(float) : 0);
     CKH(cudaMalloc((void**)&h->flags, flag_bytes));
     if (p->nranks_y > 1) h->gcol = (float*)((char*)h->flags + GCOL_OFFSET);
-    CKH(cudaMalloc((void**)&h->d_resid, sizeof(unsigned)));
+    CKH(cudaMalloc((void**)&h->d_resid, 2 * sizeof(unsigned)));
     CKH(cudaMalloc((void**)&h->d_edge_count, 4 * sizeof(unsigned)));
-    CKH(cudaHostAlloc((void**)&h->h_resid, sizeof(unsigned), cudaHostAllocDefault));
+    CKH(cudaHostAlloc((void**)&h->h_resid, 2 * sizeof(unsigned), cudaHostAllocDefault));
     CKH(cudaHostAlloc((void**)&h->h_status, sizeof(int), cudaHostAllocMapped));
     *h->h_status = 0;
     CKH(cudaHostGetDevicePointer((void**)&h->d_status, h->h_status, 0));
@@ -396,12 +413,12 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     h->own_stream = true;
     // heat_upload / heat_init_inidat overwrite every row and column of the field; only the padding columns
     // [nyloc, pitch), which the kernels load and copy through, must hold something harmless
-    if (h->pitch > h->nyloc)
+    if (h->pitch > (int64_t)h->nyloc * h->es)
         for (int k = 0; k < 2; k++)
-            CKH(cudaMemset2DAsync(h->buf[k] + h->nyloc, h->pitch * sizeof(float), 0, (size_t)(h->pitch - h->nyloc) * sizeof(float),
-                                  h->nloc, h->stream));
+            CKH(cudaMemset2DAsync(h->buf[k] + (size_t)h->nyloc * h->es, h->pitch * sizeof(float), 0,
+                                  (size_t)(h->pitch - (int64_t)h->nyloc * h->es) * sizeof(float), h->nloc, h->stream));
     CKH(cudaMemsetAsync(h->flags, 0, flag_bytes, h->stream));
-    CKH(cudaMemsetAsync(h->d_resid, 0, sizeof(unsigned), h->stream));
+    CKH(cudaMemsetAsync(h->d_resid, 0, 2 * sizeof(unsigned), h->stream));
     CKH(cudaMemsetAsync(h->d_edge_count, 0, 4 * sizeof(unsigned), h->stream));
     if (env_int("HEAT_PROFILE_WAIT", 0) != 0) {
         CKH(cudaMalloc((void**)&h->d_wait_prof, 8 * sizeof(unsigned long long)));
@@ -420,7 +437,10 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     h->serpentine = env_int("HEAT_SERPENTINE", 1) != 0;
     {
         const char* v = getenv("HEAT_K1_VARIANT");
-        h->k1_bulk = v && !strcmp(v, "bulk");
+        h->k1_variant = !v || !*v || !strcmp(v, "auto") ? 2 : !strcmp(v, "bulk") ? 1 : 0;
+#ifdef HEAT_BOUNDS_CHECK
+        h->k1_variant = 0; // the checked build watches the loads of the register-streaming kernels
+#endif
     }
     h->cols_first = env_int("HEAT_COLS_FIRST", 0);
     if (h->cols_first < 0) h->cols_first = 0;
@@ -431,6 +451,7 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     h->use_graphs = env_int("HEAT_GRAPHS", 1) != 0;
     h->use_resident = env_int("HEAT_RESIDENT", 1) != 0;
 #endif
+    if (h->es == 2) h->use_resident = false; // K5 keeps a float field in shared memory
     *out = h;
     return HEAT_OK;
 }
@@ -472,6 +493,11 @@ static void count_edge_ctas(heat_handle* h, int rows, int rpt, unsigned grid_x, 
     h->sync_args.count[2] = h->sync_args.count[3] = tiles; // one west-edge and one east-edge CTA per tile row
 }
 
+#ifndef HEAT_BULK_ROWS
+#define HEAT_BULK_ROWS 8 // tile height of the shared-memory staged kernel
+#endif
+static const int64_t BULK_MIN_PITCH = 16384; // floats per row from which "auto" stages tiles in shared memory
+
 template <int ARITH, bool RESID>
 static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, float* peer_n, float* peer_s, int reverse)
 {
@@ -486,6 +512,27 @@ static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, fl
     if ((rows + rpt - 1) / rpt > 65535) rpt = (rows + 65534) / 65535; // grid.y limit: taller tiles
     dim3 grid((unsigned)((h->pitch / 4 + THREADS - 1) / THREADS), (unsigned)((rows + rpt - 1) / rpt));
     count_edge_ctas(h, rows, rpt, grid.x, grid.y);
+    // K1b, the shared-memory staged variant: measured faster than the register-streaming kernel where rows are long
+    // (16384 floats and more), slower below; "auto" picks by row length.  Row strips and the residual are supported,
+    // column blocks are not.
+    const bool bulk = h->p.nranks_y == 1 && (h->k1_variant == 1 || (h->k1_variant == 2 && h->pitch >= BULK_MIN_PITCH));
+    if (bulk) {
+        constexpr int ROWS = HEAT_BULK_ROWS;
+        if (h->ghost <= ROWS && (rows + ROWS - 1) / ROWS <= 65535) {
+            dim3 g((unsigned)((h->pitch / 4 + THREADS - 1) / THREADS), (unsigned)((rows + ROWS - 1) / ROWS));
+            count_edge_ctas(h, rows, ROWS, g.x, g.y);
+            if (h->sync_args.counters)
+                heat_step_bulk<ARITH, RESID, ROWS, THREADS, true><<<g, THREADS, 0, h->stream>>>(
+                    in, out, h->upd_lo, h->upd_hi, ny, h->pitch, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse,
+                    h->sync_args, h->d_status);
+            else
+                heat_step_bulk<ARITH, RESID, ROWS, THREADS, false><<<g, THREADS, 0, h->stream>>>(
+                    in, out, h->upd_lo, h->upd_hi, ny, h->pitch, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse,
+                    h->sync_args, h->d_status);
+            h->launches++;
+            return cudaGetLastError();
+        }
+    }
     if (h->p.nranks_y > 1) { // 2-D blocks: column neighbours too
         const int M = h->col_args.edge_first, xe = ((ny - 2) >> 2) / THREADS;
         if (M > 1 && h->sync_args.counters && cols_first_active((int)grid.x, (int)grid.y, xe))
@@ -503,12 +550,7 @@ static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, fl
         heat_step_vec<ARITH, RESID, THREADS, UNROLL, true><<<grid, THREADS, 0, h->stream>>>(
             in, out, h->upd_lo, h->upd_hi, ny, h->pitch, rpt, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse,
             h->sync_args);
-    else if (!RESID && h->k1_bulk && !peer_n && !peer_s) {
-        constexpr int ROWS = 8;
-        dim3 g((unsigned)((h->pitch / 4 + THREADS - 1) / THREADS), (unsigned)((rows + ROWS - 1) / ROWS));
-        heat_step_bulk<ARITH, ROWS, THREADS><<<g, THREADS, 0, h->stream>>>(in, out, h->upd_lo, h->upd_hi, ny, h->pitch, h->p.cx, h->p.cy,
-                                                                          reverse, h->d_status);
-    } else
+    else
         heat_step_vec<ARITH, RESID, THREADS, UNROLL, false><<<grid, THREADS, 0, h->stream>>>(
             in, out, h->upd_lo, h->upd_hi, ny, h->pitch, rpt, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse,
             h->sync_args);
@@ -579,9 +621,41 @@ static cudaError_t launch_tb(heat_handle* h, int T, const float* in, float* out,
 #undef TB_CASE
 }
 
+// double-precision grids: one kernel, contraction chosen by `arith` (HEAT_F32_FMA = contract like nvcc, else round every op)
+template <bool FMA, bool RESID>
+static cudaError_t launch_step_f64_t(heat_handle* h, const float* in, float* out, float* peer_n, float* peer_s, int reverse)
+{
+    const int rows = h->upd_hi - h->upd_lo, ny = h->nyloc;
+    if (rows < 1 || ny < 3) return cudaSuccess;
+    const int64_t epitch = h->pitch / 2;
+    int rpt = pick_rows_per_tile(h, 128);
+    if (rpt < h->ghost) rpt = h->ghost;
+    if ((rows + rpt - 1) / rpt > 65535) rpt = (rows + 65534) / 65535;
+    dim3 grid((unsigned)((epitch / 2 + 127) / 128), (unsigned)((rows + rpt - 1) / rpt));
+    count_edge_ctas(h, rows, rpt, grid.x, grid.y);
+    const double cx = (double)h->p.cx, cy = (double)h->p.cy; // struct Parms stays float (M:29-32): the constants are 0.1f widened
+    if (h->sync_args.counters)
+        heat_step_f64<FMA, RESID, true><<<grid, 128, 0, h->stream>>>((const double*)in, (double*)out, h->upd_lo, h->upd_hi, ny, epitch, rpt,
+                                                                    cx, cy, (unsigned long long*)h->d_resid, (double*)peer_n,
+                                                                    (double*)peer_s, h->ghost, reverse, h->sync_args);
+    else
+        heat_step_f64<FMA, RESID, false><<<grid, 128, 0, h->stream>>>((const double*)in, (double*)out, h->upd_lo, h->upd_hi, ny, epitch, rpt,
+                                                                     cx, cy, (unsigned long long*)h->d_resid, (double*)peer_n,
+                                                                     (double*)peer_s, h->ghost, reverse, h->sync_args);
+    h->launches++;
+    return cudaGetLastError();
+}
+
 static cudaError_t launch_step(heat_handle* h, bool resid, const float* in, float* out, float* peer_n, float* peer_s,
                                int reverse)
 {
+    if (h->es == 2) {
+        const bool fma = h->p.arith == HEAT_F32_FMA;
+        return fma ? (resid ? launch_step_f64_t<true, true>(h, in, out, peer_n, peer_s, reverse)
+                            : launch_step_f64_t<true, false>(h, in, out, peer_n, peer_s, reverse))
+                   : (resid ? launch_step_f64_t<false, true>(h, in, out, peer_n, peer_s, reverse)
+                            : launch_step_f64_t<false, false>(h, in, out, peer_n, peer_s, reverse));
+    }
     switch (h->p.arith * 2 + (resid ? 1 : 0)) {
     case 0: return launch_step_t<HEAT_ARITH_F32_FMA, false>(h, in, out, peer_n, peer_s, reverse);
     case 1: return launch_step_t<HEAT_ARITH_F32_FMA, true>(h, in, out, peer_n, peer_s, reverse);
@@ -632,7 +706,7 @@ static int enqueue_update(heat_handle* h, bool resid, int fused = 1)
             h->col_args.ge_in = h->gcol + (h->cur * 2 + 1) * n;
         }
     }
-    if (resid) CK(cudaMemsetAsync(h->d_resid, 0, sizeof(unsigned), h->stream));
+    if (resid) CK(cudaMemsetAsync(h->d_resid, 0, 2 * sizeof(unsigned), h->stream));
     // flag-ordered strips (one process per GPU): the wait and the signal are fused into the pass
     h->sync_args = strip_sync{};
     if (strips && !local) {
@@ -929,6 +1003,22 @@ extern "C" int heat_set_allreduce_max(heat_handle* h, heat_allreduce_max_fn fn, 
     return HEAT_OK;
 }
 
+// max|old-new| as the float the convergence test compares (a double grid's maximum is rounded UP to float, so
+// that `r < eps` can never hold for a double residual that is not below eps)
+static float resid_value(const heat_handle* h)
+{
+    if (h->es == 2) {
+        double d;
+        memcpy(&d, h->h_resid, sizeof d);
+        float f = (float)d;
+        if ((double)f < d) f = nextafterf(f, INFINITY);
+        return f;
+    }
+    float f;
+    memcpy(&f, h->h_resid, sizeof f);
+    return f;
+}
+
 // The time loop (C:204-238 / M:159-265) over one strip or over all strips of this process.
 extern "C" int heat_group_run(heat_handle** hs, int n, int steps, int* updates_done, int* converged)
 {
@@ -969,7 +1059,7 @@ extern "C" int heat_group_run(heat_handle** hs, int n, int steps, int* updates_d
             if (rc) return rc;
             if (check) {
                 // one 4-byte read-back per K updates: the only host sync in the loop
-                CK(cudaMemcpyAsync(hs[k]->h_resid, hs[k]->d_resid, sizeof(unsigned), cudaMemcpyDeviceToHost, hs[k]->stream));
+                CK(cudaMemcpyAsync(hs[k]->h_resid, hs[k]->d_resid, 2 * sizeof(unsigned), cudaMemcpyDeviceToHost, hs[k]->stream));
                 CK(cudaEventRecord(hs[k]->ev_resid, hs[k]->stream));
             }
         }
@@ -978,9 +1068,7 @@ extern "C" int heat_group_run(heat_handle** hs, int n, int steps, int* updates_d
             float r = 0.0f;
             for (int k = 0; k < n; k++) {
                 CK(cudaEventSynchronize(hs[k]->ev_resid));
-                float rk;
-                memcpy(&rk, hs[k]->h_resid, sizeof rk);
-                r = fmaxf(r, rk);
+                r = fmaxf(r, resid_value(hs[k]));
             }
             // strips in other processes: one small max-allreduce (replaces MPI_Allreduce(LAND), M:255)
             if (h0->allreduce && h0->allreduce(&r, h0->allreduce_ctx) != 0)
@@ -1049,15 +1137,19 @@ extern "C" int heat_residual(heat_handle* h, float* residual)
 {
     if (!h || !residual) return fail(HEAT_E_INVALID, "heat_residual: bad arguments");
     CK(cudaSetDevice(h->p.device));
-    CK(cudaMemsetAsync(h->d_resid, 0, sizeof(unsigned), h->stream));
+    CK(cudaMemsetAsync(h->d_resid, 0, 2 * sizeof(unsigned), h->stream));
     if (h->upd_hi > h->upd_lo && h->nyloc >= 3) {
-        heat_absdiff_max<<<h->sm_count * 8, 256, 0, h->stream>>>(h->buf[0], h->buf[1], h->upd_lo, h->upd_hi, h->nyloc, h->pitch, h->d_resid);
+        if (h->es == 2)
+            heat_absdiff_max_f64<<<h->sm_count * 8, 256, 0, h->stream>>>((const double*)h->buf[0], (const double*)h->buf[1], h->upd_lo,
+                                                                        h->upd_hi, h->nyloc, h->pitch / 2, (unsigned long long*)h->d_resid);
+        else
+            heat_absdiff_max<<<h->sm_count * 8, 256, 0, h->stream>>>(h->buf[0], h->buf[1], h->upd_lo, h->upd_hi, h->nyloc, h->pitch, h->d_resid);
         h->launches++;
         CK(cudaGetLastError());
     }
-    CK(cudaMemcpyAsync(h->h_resid, h->d_resid, sizeof(unsigned), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(h->h_resid, h->d_resid, 2 * sizeof(unsigned), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
-    memcpy(residual, h->h_resid, sizeof(float));
+    *residual = resid_value(h);
     return HEAT_OK;
 }
 
@@ -1130,15 +1222,32 @@ static int upload_from(heat_handle* h, const void* src, int src_first_row, cudaM
     CK(cudaSetDevice(h->p.device));
     int rc = quiesce_neighbours(h);
     if (rc) return rc;
-    const float* rows = (const float*)src + (size_t)(h->lo - src_first_row) * h->p.ny + h->lo_c;
+    const size_t esz = (size_t)h->es * sizeof(float); // bytes per element
+    const char* rows = (const char*)src + ((size_t)(h->lo - src_first_row) * h->p.ny + h->lo_c) * esz;
     // C:197-198: the initial field goes into both buffers -- over PCIe once, the second copy on the device
-    CK(cudaMemcpy2DAsync(h->buf[0], h->pitch * sizeof(float), rows, (size_t)h->p.ny * sizeof(float),
-                         (size_t)h->nyloc * sizeof(float), h->nloc, kind, h->stream));
+    CK(cudaMemcpy2DAsync(h->buf[0], h->pitch * sizeof(float), rows, (size_t)h->p.ny * esz, (size_t)h->nyloc * esz, h->nloc, kind,
+                         h->stream));
     CK(cudaMemcpyAsync(h->buf[1], h->buf[0], (size_t)h->nloc * h->pitch * sizeof(float), cudaMemcpyDeviceToDevice, h->stream));
     return after_upload(h);
 }
 
-extern "C" int heat_upload(heat_handle* h, const float* full_grid) { return upload_from(h, full_grid, 0, cudaMemcpyHostToDevice); }
+static int wrong_type(const heat_handle* h, int want_es, const char* fn)
+{
+    if (h && h->es != want_es)
+        return fail(HEAT_E_STATE, "%s: the handle's grid is %s", fn, h->es == 2 ? "double (use the _f64 entry points)" : "float");
+    return HEAT_OK;
+}
+
+extern "C" int heat_upload(heat_handle* h, const float* full_grid)
+{
+    int rc = wrong_type(h, 1, "heat_upload");
+    return rc ? rc : upload_from(h, full_grid, 0, cudaMemcpyHostToDevice);
+}
+extern "C" int heat_upload_f64(heat_handle* h, const double* full_grid)
+{
+    int rc = wrong_type(h, 2, "heat_upload_f64");
+    return rc ? rc : upload_from(h, full_grid, 0, cudaMemcpyHostToDevice);
+}
 extern "C" int heat_upload_device(heat_handle* h, const void* d_full_grid) { return upload_from(h, d_full_grid, 0, cudaMemcpyDeviceToDevice); }
 
 extern "C" int heat_init_inidat(heat_handle* h)
@@ -1151,14 +1260,30 @@ extern "C" int heat_init_inidat(heat_handle* h)
         int rc = quiesce_neighbours(h);
         if (rc) return rc;
     }
-    heat_inidat_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(h->buf[0], h->buf[1], h->p.nx, h->p.ny, h->lo, h->nloc, h->pitch,
-                                                               h->lo_c, h->nyloc);
+    if (h->es == 2)
+        heat_inidat_f64_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>((double*)h->buf[0], (double*)h->buf[1], h->p.nx, h->p.ny, h->lo,
+                                                                       h->nloc, h->pitch / 2, h->lo_c, h->nyloc);
+    else
+        heat_inidat_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(h->buf[0], h->buf[1], h->p.nx, h->p.ny, h->lo, h->nloc, h->pitch,
+                                                                   h->lo_c, h->nyloc);
     h->launches++;
     CK(cudaGetLastError());
     return after_upload(h);
 }
 
+static int download_to(heat_handle* h, void* full_grid);
 extern "C" int heat_download(heat_handle* h, float* full_grid)
+{
+    int rc = wrong_type(h, 1, "heat_download");
+    return rc ? rc : download_to(h, full_grid);
+}
+extern "C" int heat_download_f64(heat_handle* h, double* full_grid)
+{
+    int rc = wrong_type(h, 2, "heat_download_f64");
+    return rc ? rc : download_to(h, full_grid);
+}
+
+static int download_to(heat_handle* h, void* full_grid)
 {
     if (!h || !full_grid) return fail(HEAT_E_INVALID, "heat_download: bad arguments");
     CK(cudaSetDevice(h->p.device));
@@ -1168,9 +1293,10 @@ extern "C" int heat_download(heat_handle* h, float* full_grid)
     }
     // only the rows and columns this block owns (ghost rows/columns belong to the neighbours)
     const int first = h->row0 - h->lo, firstc = h->col0 - h->lo_c;
-    CK(cudaMemcpy2DAsync(full_grid + (size_t)h->row0 * h->p.ny + h->col0, (size_t)h->p.ny * sizeof(float),
-                         h->buf[h->cur] + (size_t)first * h->pitch + firstc, h->pitch * sizeof(float),
-                         (size_t)h->cols_own * sizeof(float), h->rows_own, cudaMemcpyDeviceToHost, h->stream));
+    const size_t esz = (size_t)h->es * sizeof(float);
+    CK(cudaMemcpy2DAsync((char*)full_grid + ((size_t)h->row0 * h->p.ny + h->col0) * esz, (size_t)h->p.ny * esz,
+                         h->buf[h->cur] + (size_t)first * h->pitch + (size_t)firstc * h->es, h->pitch * sizeof(float),
+                         (size_t)h->cols_own * esz, h->rows_own, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     return HEAT_OK;
 }
@@ -1180,6 +1306,7 @@ extern "C" int heat_upload_local(heat_handle* h, const float* local_rows)
 {
     if (!h || !local_rows) return fail(HEAT_E_INVALID, "heat_upload_local: bad arguments");
     if (h->p.nranks_y > 1) return fail(HEAT_E_STATE, "heat_upload_local: row strips only (column blocks use heat_upload)");
+    if (h->es != 1) return wrong_type(h, 1, "heat_upload_local");
     // same copy as heat_upload, from a source whose first row is the strip's first local row
     return upload_from(h, local_rows, h->lo, cudaMemcpyHostToDevice);
 }
@@ -1188,6 +1315,7 @@ extern "C" int heat_download_local(heat_handle* h, float* own_rows)
 {
     if (!h || !own_rows) return fail(HEAT_E_INVALID, "heat_download_local: bad arguments");
     if (h->p.nranks_y > 1) return fail(HEAT_E_STATE, "heat_download_local: row strips only (column blocks use heat_download)");
+    if (h->es != 1) return wrong_type(h, 1, "heat_download_local");
     CK(cudaSetDevice(h->p.device));
     {
         int rc = ensure_loaded(h);
@@ -1205,7 +1333,7 @@ extern "C" int heat_device_view(heat_handle* h, int which, void** d_ptr, int64_t
 {
     if (!h || (which != 0 && which != 1)) return fail(HEAT_E_INVALID, "heat_device_view: bad arguments");
     if (d_ptr) *d_ptr = h->buf[which == 0 ? h->cur : 1 - h->cur];
-    if (pitch) *pitch = h->pitch;
+    if (pitch) *pitch = h->pitch / h->es;
     if (local_rows) *local_rows = h->nloc;
     if (first_global_row) *first_global_row = h->lo;
     return HEAT_OK;
@@ -1235,13 +1363,14 @@ static bool solve_can_stream(const heat_handle* h, long long updates)
     return passes * T * 4 <= h->p.nx; // the skew costs passes*T extra rows of pipeline: keep it under a quarter
 }
 
-static int solve_streamed(heat_handle* h, float* grid, long long updates)
+static int solve_streamed(heat_handle* h, void* grid_, long long updates)
 {
     const int nx = h->p.nx, ny = h->p.ny, T = h->p.temporal_block;
     const int nfused = (int)(T > 1 ? updates / T : 0), P = (int)(T > 1 ? updates / T + updates % T : updates);
     const int s = T;             // rows a pass is shifted against the one before: >= what a pass reads beyond its rows
     const long long S = (long long)P * s;
-    const size_t row_bytes = (size_t)ny * sizeof(float);
+    const size_t row_bytes = (size_t)ny * h->es * sizeof(float);
+    char* const grid = (char*)grid_;
     // band height: a sixteenth of the field, between 8 and 128 MiB (small enough to fill the pipeline quickly, large
     // enough that a pass over one band is several waves of CTAs); HEAT_SOLVE_BAND_ROWS overrides
     size_t band_bytes = (size_t)nx * row_bytes / 16;
@@ -1275,7 +1404,7 @@ static int solve_streamed(heat_handle* h, float* grid, long long updates)
     for (long long i = 0; !rc && sent < nx - 1; i++) {
         const long long b0 = i * B, b1 = (i + 1) * B < nx ? (i + 1) * B : nx;
         if (b0 < nx) { // a real band: rows [b0, b1) arrive in buf[0]
-            CKS(cudaMemcpy2DAsync(h->buf[0] + b0 * h->pitch, h->pitch * sizeof(float), grid + b0 * ny, row_bytes, row_bytes,
+            CKS(cudaMemcpy2DAsync(h->buf[0] + b0 * h->pitch, h->pitch * sizeof(float), grid + b0 * row_bytes, row_bytes, row_bytes,
                                   (size_t)(b1 - b0), cudaMemcpyHostToDevice, in_s));
             CKS(cudaEventRecord(ev_in, in_s));
             CKS(cudaStreamWaitEvent(h->stream, ev_in, 0));
@@ -1302,7 +1431,7 @@ static int solve_streamed(heat_handle* h, float* grid, long long updates)
         if (done > sent) {
             CKS(cudaEventRecord(ev_done, h->stream));
             CKS(cudaStreamWaitEvent(out_s, ev_done, 0));
-            CKS(cudaMemcpy2DAsync(grid + sent * ny, row_bytes, fin + sent * h->pitch, h->pitch * sizeof(float), row_bytes,
+            CKS(cudaMemcpy2DAsync(grid + sent * row_bytes, row_bytes, fin + sent * h->pitch, h->pitch * sizeof(float), row_bytes,
                                   (size_t)(done - sent), cudaMemcpyDeviceToHost, out_s));
             sent = done;
         }
@@ -1332,9 +1461,21 @@ static int solve_streamed(heat_handle* h, float* grid, long long updates)
     return rc;
 }
 
+static int solve_host(const heat_params* p, void* grid, int es, int* updates_done, int* converged);
 extern "C" int heat_solve(const heat_params* p, float* grid, int* updates_done, int* converged)
 {
+    return solve_host(p, grid, 1, updates_done, converged);
+}
+extern "C" int heat_solve_f64(const heat_params* p, double* grid, int* updates_done, int* converged)
+{
+    return solve_host(p, grid, 2, updates_done, converged);
+}
+
+static int solve_host(const heat_params* p, void* grid, int es, int* updates_done, int* converged)
+{
     if (!grid) return fail(HEAT_E_INVALID, "heat_solve: null grid");
+    if (p && (p->grid_type == HEAT_GRID_F64) != (es == 2))
+        return fail(HEAT_E_INVALID, "heat_solve: params.grid_type does not match the entry point (heat_solve = float, heat_solve_f64 = double)");
     if (p && (p->nranks != 1 || p->nranks_y != 1))
         return fail(HEAT_E_INVALID, "heat_solve: one strip only (use the handle API for strips)");
     const bool timing = env_int("HEAT_TIMING", 0) != 0;
@@ -1359,11 +1500,11 @@ extern "C" int heat_solve(const heat_params* p, float* grid, int* updates_done, 
         }
         t2 = t1, t3 = t4 = now();
     } else {
-        rc = heat_upload(h, grid);
+        rc = upload_from(h, grid, 0, cudaMemcpyHostToDevice);
         t2 = now();
         if (!rc) rc = heat_run(h, p->steps, updates_done, converged);
         t3 = now();
-        if (!rc) rc = heat_download(h, grid);
+        if (!rc) rc = download_to(h, grid);
         t4 = now();
     }
     const float loop_ms = h->last_ms;

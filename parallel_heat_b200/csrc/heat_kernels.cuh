@@ -64,7 +64,12 @@ __device__ __forceinline__ float upd(float c, float n, float s, float e, float w
 // integer way when the vote allows it (0 = none: the scalar form; 1 = the centre value; 2 = centre and
 // the N+S sum; 3 = all).  The final double->float rounding always stays a conversion instruction.
 #ifndef HEAT_F64_WIDEN_INT
-#define HEAT_F64_WIDEN_INT 0
+#define HEAT_F64_WIDEN_INT 1
+#endif
+// On the same fast path 2u can be had without the FP64 pipe as well: doubling a normal double is +1 on its
+// exponent field (the widened float's exponent is at most 1150, far from overflow).  HEAT_F64_INT_DOUBLE.
+#ifndef HEAT_F64_INT_DOUBLE
+#define HEAT_F64_INT_DOUBLE 0
 #endif
 
 __device__ __forceinline__ double widen_normal(float v)
@@ -100,7 +105,11 @@ __device__ __forceinline__ float4 upd4_f64mix(const float4& c, const float4& n, 
 #pragma unroll
         for (int i = 0; i < 4; i++) {
             const double cd = widen_normal(cv[i]);
+#if HEAT_F64_INT_DOUBLE
+            const double c2 = __hiloint2double(__double2hiint(cd) + 0x00100000, __double2loint(cd));
+#else
             const double c2 = __dadd_rn(cd, cd);
+#endif
             const double t1 = __dsub_rn(NINT > 1 ? widen_normal(sn[i]) : (double)sn[i], c2);
             const double t2 = __dsub_rn(NINT > 2 ? widen_normal(ew[i]) : (double)ew[i], c2);
             o[i] = __double2float_rn(__dadd_rn(__dadd_rn(cd, __dmul_rn(dcx, t1)), __dmul_rn(dcy, t2)));
@@ -122,9 +131,15 @@ __device__ __forceinline__ float4 upd4_f64mix(const float4& c, const float4& n, 
 // FADD2 / FMUL2 / FFMA2 do two IEEE-rounded float operations per instruction on the register pairs a float4
 // already sits in after LDG.128.  Same operations in the same order as upd<>, hence the same bits; only the
 // four E+W sums stay scalar (their operands straddle the pairs): 16 floating-point instructions per float4
-// instead of 28.  Build-time switch HEAT_PACKED_F32 (K1's plain path and K4's fast path).
-#ifndef HEAT_PACKED_F32
-#define HEAT_PACKED_F32 0
+// instead of 28.  Measured (round 2, one B200): nothing for K1 (852 vs 852 GLUP/s at 8192^2, 848 vs 851 at
+// 65536^2: the kernel waits for HBM, not for issue slots), but K4, which is FP32-issue-bound, gains: T=4 at
+// 32768^2 2620 -> 2670 GLUP/s (F32_FMA) and 2345 -> 2666 (F32_NOFMA, whose unfused multiplies and adds pack
+// best), 8192^2 2159 -> 2224.  So packed is the default in K4 (HEAT_PACKED_K4) and off in K1 (HEAT_PACKED_K1).
+#ifndef HEAT_PACKED_K1
+#define HEAT_PACKED_K1 0
+#endif
+#ifndef HEAT_PACKED_K4
+#define HEAT_PACKED_K4 1
 #endif
 typedef unsigned long long f32x2;
 __device__ __forceinline__ f32x2 pk2(float a, float b)
@@ -187,12 +202,12 @@ __device__ __forceinline__ float4 upd4_packed(const float4& c, const float4& n, 
 
 // One float4 of a row whose four columns are all interior, E/W neighbours across the float4 given (all lanes of
 // the warp must call this together: the MPI_F64MIX form votes).
-template <int ARITH>
+template <int ARITH, bool PACKED = (HEAT_PACKED_K1 != 0)>
 __device__ __forceinline__ float4 upd_quad(const float4& c, const float4& n, const float4& s, float wl, float er, float cx, float cy)
 {
     if constexpr (ARITH == HEAT_ARITH_F64MIX && HEAT_F64_WIDEN_INT > 0) {
         return upd4_f64mix<HEAT_F64_WIDEN_INT>(c, n, s, wl, er, cx, cy);
-    } else if constexpr (ARITH != HEAT_ARITH_F64MIX && HEAT_PACKED_F32) {
+    } else if constexpr (ARITH != HEAT_ARITH_F64MIX && PACKED) {
         return upd4_packed<ARITH>(c, n, s, wl, er, cx, cy);
     } else {
         float4 o;
@@ -645,23 +660,30 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
 
 // ------------------------------------------------------------------ K1b: the same update from a shared-memory tile
 // The alternative north_star names: a tile with its halo rows is staged in shared memory by the bulk-copy
-// engine (cp.async.bulk, one copy per row, completion on an mbarrier), then every thread computes its float4
-// column of the tile from shared memory.  One tile per CTA, no pipelining inside the CTA: the other CTAs of the
-// SM (21 KB of shared memory each) cover the copy latency.  HEAT_K1_VARIANT=bulk, single strip, no residual.
-// It moves exactly the bytes K1 moves and adds an LDS per LDG, so it is here to be MEASURED against K1.
-template <int ARITH, int ROWS, int THREADS>
+// engine (cp.async.bulk, one copy per row, completion on an mbarrier; SASS: UBLKCP), then every thread computes
+// its float4 column of the tile from shared memory (E/W neighbours by shuffle, across the warp edge from the
+// tile).  One tile per CTA, no pipelining inside the CTA: the other CTAs of the SM (ROWS+2 rows of 2080 bytes
+// each) cover the copy latency.  Same bytes over HBM as K1; what changes is who issues the loads: one thread
+// issues ROWS+2 row copies of 2 KB instead of 128 threads issuing 16-byte loads.  Measured (round 2, one B200,
+// 20-update repetitions): 8192^2 850 vs 852 GLUP/s for K1, 16384^2 862 vs 854, 65536^2 865 vs 851 -- it wins
+// where rows are long, so HEAT_K1_VARIANT=auto (the default) takes it for rows of 16384 floats and more.
+// Everything K1 does besides is here too: residual (K2), neighbour strips' ghost rows and step flags (K3).
+template <int ARITH, bool RESID, int ROWS, int THREADS, bool SYNC>
 __global__ void __launch_bounds__(THREADS)
 heat_step_bulk(const float* __restrict__ in, float* __restrict__ out, int row_lo, int row_hi, int ny, int64_t pitch, float cx,
-               float cy, int reverse, int* __restrict__ status)
+               float cy, unsigned* __restrict__ resid, float* peer_n, float* peer_s, int ghost, int reverse, strip_sync sy,
+               int* __restrict__ status)
 {
     namespace ptx = cuda::ptx;
     constexpr int W = THREADS * 4, HALO = 4, SW = W + 2 * HALO; // staged row: 4 columns of halo on either side
     __shared__ __align__(128) float tile[(ROWS + 2) * SW];
     __shared__ __align__(8) uint64_t bar;
-    const int npitch = (int)pitch, tid = threadIdx.x;
+    const unsigned FULL = 0xffffffffu;
+    const int npitch = (int)pitch, tid = threadIdx.x, lane = tid & 31;
     const int ntiles = gridDim.y;
-    const int t = reverse ? ntiles - 1 - (int)blockIdx.y : (int)blockIdx.y;
+    const int t = tile_of_block<SYNC>((int)blockIdx.y, ntiles, reverse);
     const int r0 = row_lo + t * ROWS, r1 = min(r0 + ROWS, row_hi), nrows = r1 - r0;
+    const bool edge_n = r0 < row_lo + ghost, edge_s = r1 > row_hi - ghost;
     const int col0 = blockIdx.x * W;
     // staged columns [c_lo, c_hi) of rows r0-1 .. r1; column c sits at tile[row * SW + (c - (col0 - HALO))]
     const int c_lo = max(col0 - HALO, 0), c_hi = min(col0 + W + HALO, npitch);
@@ -670,6 +692,7 @@ heat_step_bulk(const float* __restrict__ in, float* __restrict__ out, int row_lo
         ptx::mbarrier_init(&bar, 1);
         ptx::fence_proxy_async(ptx::space_shared); // the barrier's initialisation must be visible to the copy engine
     }
+    if (SYNC) strip_wait(sy, edge_n, edge_s); // the ghost rows this tile reads are the neighbour's previous pass
     __syncthreads();
     if (tid == 0) {
         ptx::mbarrier_arrive_expect_tx(ptx::sem_release, ptx::scope_cta, ptx::space_shared, &bar, row_bytes * (unsigned)(nrows + 2));
@@ -685,31 +708,46 @@ heat_step_bulk(const float* __restrict__ in, float* __restrict__ out, int row_lo
             break;
         }
     }
+    float m = 0.0f;
     const int col = col0 + tid * 4;
-    if (col >= npitch) return;
-    const bool kx = (col == 0) || (col >= ny - 1), ky = (col + 1 >= ny - 1), kz = (col + 2 >= ny - 1), kw = (col + 3 >= ny - 1);
-    const float* c_row = tile + SW + HALO + tid * 4; // row r0, my first column
-    float4 n = *reinterpret_cast<const float4*>(c_row - SW);
-    float4 c = *reinterpret_cast<const float4*>(c_row);
-    float* q = out + (int64_t)r0 * pitch + col;
-    for (int i = 0; i < nrows; i++) {
-        const float4 s = *reinterpret_cast<const float4*>(c_row + SW);
-        const float wl = c_row[-1], er = c_row[4]; // garbage only where the result is a ring / padding column
-        float4 o;
-        o.x = upd<ARITH>(c.x, n.x, s.x, c.y, wl, cx, cy);
-        o.y = upd<ARITH>(c.y, n.y, s.y, c.z, c.x, cx, cy);
-        o.z = upd<ARITH>(c.z, n.z, s.z, c.w, c.y, cx, cy);
-        o.w = upd<ARITH>(c.w, n.w, s.w, er, c.z, cx, cy);
-        if (kx) o.x = c.x;
-        if (ky) o.y = c.y;
-        if (kz) o.z = c.z;
-        if (kw) o.w = c.w;
-        st4(q, o);
-        n = c;
-        c = s;
-        c_row += SW;
-        q += pitch;
+    const bool live = col < npitch;
+    if (col - lane * 4 < npitch) { // else the whole warp is beyond the row (warp-uniform: the shuffles stay converged)
+        const bool kx = (col == 0) || (col >= ny - 1), ky = (col + 1 >= ny - 1), kz = (col + 2 >= ny - 1), kw = (col + 3 >= ny - 1);
+        const float* c_row = tile + SW + HALO + tid * 4; // row r0, my first column
+        float4 n = *reinterpret_cast<const float4*>(c_row - SW);
+        float4 c = *reinterpret_cast<const float4*>(c_row);
+        float* q = out + (int64_t)r0 * pitch + col;
+        for (int i = 0; i < nrows; i++) {
+            const float4 s = *reinterpret_cast<const float4*>(c_row + SW);
+            float wl = __shfl_up_sync(FULL, c.w, 1);
+            float er = __shfl_down_sync(FULL, c.x, 1);
+            if (lane == 0) wl = c_row[-1];  // from the tile's halo columns; garbage only where the result is a ring / padding column
+            if (lane == 31) er = c_row[4];
+            float4 o = upd_quad<ARITH>(c, n, s, wl, er, cx, cy);
+            if (kx) o.x = c.x;
+            if (ky) o.y = c.y;
+            if (kz) o.z = c.z;
+            if (kw) o.w = c.w;
+            if (live) {
+                st4(q, o);
+                // K3: the first / last `ghost` updated rows are the neighbours' ghost rows
+                if (peer_n && r0 + i < row_lo + ghost) st4(peer_n + (int64_t)(r0 + i - row_lo) * pitch + col, o);
+                if (peer_s && r0 + i >= row_hi - ghost) st4(peer_s + (int64_t)(r0 + i - (row_hi - ghost)) * pitch + col, o);
+            }
+            if (RESID) {
+                m = fmaxf(m, fabsf(__fsub_rn(c.x, o.x)));
+                m = fmaxf(m, fabsf(__fsub_rn(c.y, o.y)));
+                m = fmaxf(m, fabsf(__fsub_rn(c.z, o.z)));
+                m = fmaxf(m, fabsf(__fsub_rn(c.w, o.w)));
+            }
+            n = c;
+            c = s;
+            c_row += SW;
+            q += pitch;
+        }
     }
+    if (RESID) block_max_to_global(live ? m : 0.0f, resid);
+    if (SYNC) strip_signal(sy, edge_n, edge_s);
 }
 
 // ------------------------------------------------------------------ K4 temporal blocking
@@ -731,7 +769,7 @@ __device__ __forceinline__ float4 upd4(const float4& c, const float4& n, const f
 {
     const float wl = __shfl_up_sync(0xffffffffu, c.w, 1);
     const float er = __shfl_down_sync(0xffffffffu, c.x, 1);
-    return upd_quad<ARITH>(c, n, s, wl, er, cx, cy);
+    return upd_quad<ARITH, (HEAT_PACKED_K4 != 0)>(c, n, s, wl, er, cx, cy);
 }
 
 // Fast path of K4 for a warp whose 128 columns hold no ring/padding column and whose tile is far
@@ -1063,6 +1101,154 @@ __global__ void __launch_bounds__(1024, 1) heat_resident(resident_args a)
         st4(a.out_final + g, ld4(fin + lr * W + c4 * 4));
         if (a.out_prev) st4(a.out_prev + g, ld4(prev + lr * W + c4 * 4));
     }
+}
+
+// ------------------------------------------------------------------ double-precision grids
+// The reference hard-codes `float` (M:46, C:170); this is its update with the element type widened: every value
+// and every operation in double, cx/cy the float constants promoted (struct Parms stays float, M:29-32).
+// FMA = true contracts the two multiply-adds like nvcc does for the CUDA source, false rounds every operation
+// like gcc does for the MPI source.  16 B per point-update, so the HBM roofline is half the float one in LUP/s.
+// Same structure as K1/K2/K3: lanes along iy, each thread owns 2 consecutive columns (one 16-byte access), N/C/S
+// rows in registers, E/W by shuffle, first/last `ghost` rows also stored into the neighbour strips, step flags
+// fused in.  Ring columns are written back unchanged, ring rows never written.
+template <bool FMA>
+__device__ __forceinline__ double upd64(double c, double n, double s, double e, double w, double cx, double cy)
+{
+    const double t1 = __dsub_rn(__dadd_rn(s, n), __dadd_rn(c, c));
+    const double t2 = __dsub_rn(__dadd_rn(e, w), __dadd_rn(c, c));
+    if (FMA) return __fma_rn(cy, t2, __fma_rn(cx, t1, c));
+    return __dadd_rn(__dadd_rn(c, __dmul_rn(cx, t1)), __dmul_rn(cy, t2));
+}
+
+__global__ void heat_inidat_f64_kernel(double* __restrict__ a, double* __restrict__ b, int nx, int ny, int row_lo, int nloc,
+                                       int64_t pitch, int col_lo, int nyloc)
+{
+    const int64_t total = (int64_t)nloc * pitch;
+    for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
+        const int lr = (int)(k / pitch);
+        const int ly = (int)(k - (int64_t)lr * pitch);
+        const int ix = row_lo + lr, iy = col_lo + ly;
+        double v = 0.0;
+        if (ly < nyloc) {
+            uint32_t p = (uint32_t)ix * (uint32_t)(nx - ix - 1) * (uint32_t)iy * (uint32_t)(ny - iy - 1);
+            v = (double)(int32_t)p; // the int product wraps before the conversion, whatever the element type (M:320)
+        }
+        a[k] = v;
+        b[k] = v;
+    }
+}
+
+__device__ __forceinline__ void block_max_to_global64(double m, unsigned long long* gmax)
+{
+    // non-negative doubles order like their bit patterns
+    unsigned long long bits = (unsigned long long)__double_as_longlong(m);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, bits, o);
+        bits = other > bits ? other : bits;
+    }
+    __shared__ unsigned long long smax64[32];
+    const int warp = threadIdx.x >> 5, nwarp = (blockDim.x + 31) >> 5;
+    if ((threadIdx.x & 31) == 0) smax64[warp] = bits;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long v = 0;
+        for (int w = 0; w < nwarp; w++) v = smax64[w] > v ? smax64[w] : v;
+        if (v != 0ull) atomicMax(gmax, v);
+    }
+}
+
+template <bool FMA, bool RESID, bool SYNC>
+__global__ void __launch_bounds__(128, 8)
+heat_step_f64(const double* __restrict__ in, double* __restrict__ out, int row_lo, int row_hi, int ny, int64_t pitch,
+              int rows_per_tile, double cx, double cy, unsigned long long* __restrict__ resid, double* peer_n, double* peer_s,
+              int ghost, int reverse, strip_sync sy)
+{
+    constexpr int UNROLL = 4;
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int npitch = (int)pitch;
+    int col = ((int)blockIdx.x * 128 + threadIdx.x) * 2;
+    const int ntiles = gridDim.y;
+    const int tile = tile_of_block<SYNC>((int)blockIdx.y, ntiles, reverse);
+    const int r0 = row_lo + tile * rows_per_tile;
+    const int r1 = min(r0 + rows_per_tile, row_hi);
+    const bool edge_n = r0 < row_lo + ghost, edge_s = r1 > row_hi - ghost;
+    if (SYNC) strip_wait(sy, edge_n, edge_s);
+
+    double m = 0.0;
+    const bool live = col < npitch;
+    if (col - lane * 2 < npitch) { // else the whole warp is beyond the row (warp-uniform)
+        if (!live) col = npitch - 2; // keep the lane in bounds for loads; it never stores
+        const bool kx = (col == 0) || (col >= ny - 1), ky = (col + 1 >= ny - 1); // ring / padding columns: copied through
+        const bool edge_lane = (lane == 0 && col > 0) || (lane == 31 && col + 2 < npitch);
+        const int edge_off = (lane == 0) ? -1 : 2;
+        const double* p = in + (int64_t)(r0 - 1) * pitch + col;
+        double* q = out + (int64_t)r0 * pitch + col;
+        double2 n = *reinterpret_cast<const double2*>(p);
+        double2 c = *reinterpret_cast<const double2*>(p + pitch);
+        double ec = edge_lane ? p[pitch + edge_off] : 0.0;
+        p += 2 * pitch;
+        for (int r = r0; r < r1; r += UNROLL) {
+            double2 s[UNROLL];
+            double es[UNROLL];
+#pragma unroll
+            for (int u = 0; u < UNROLL; u++) {
+                const int64_t off = (int64_t)min(u, r1 - 1 - r) * pitch; // rows past the tile: clamped, loaded, unused
+                s[u] = *reinterpret_cast<const double2*>(p + off);
+                es[u] = edge_lane ? p[off + edge_off] : 0.0;
+            }
+#pragma unroll
+            for (int u = 0; u < UNROLL; u++) {
+                if (r + u < r1) {
+                    double wl = __shfl_up_sync(FULL, c.y, 1);
+                    double er = __shfl_down_sync(FULL, c.x, 1);
+                    if (lane == 0) wl = ec;
+                    if (lane == 31) er = ec;
+                    double2 o;
+                    o.x = upd64<FMA>(c.x, n.x, s[u].x, c.y, wl, cx, cy);
+                    o.y = upd64<FMA>(c.y, n.y, s[u].y, er, c.x, cx, cy);
+                    if (kx) o.x = c.x;
+                    if (ky) o.y = c.y;
+                    if (live) {
+                        *reinterpret_cast<double2*>(q) = o;
+                        if (peer_n && r + u < row_lo + ghost)
+                            *reinterpret_cast<double2*>(peer_n + (int64_t)(r + u - row_lo) * pitch + col) = o;
+                        if (peer_s && r + u >= row_hi - ghost)
+                            *reinterpret_cast<double2*>(peer_s + (int64_t)(r + u - (row_hi - ghost)) * pitch + col) = o;
+                    }
+                    if (RESID) {
+                        m = fmax(m, fabs(__dsub_rn(c.x, o.x)));
+                        m = fmax(m, fabs(__dsub_rn(c.y, o.y)));
+                    }
+                    n = c;
+                    c = s[u];
+                    ec = es[u];
+                    q += pitch;
+                }
+            }
+            p += (int64_t)UNROLL * pitch;
+        }
+    }
+    if (RESID) block_max_to_global64(live ? m : 0.0, resid);
+    if (SYNC) strip_signal(sy, edge_n, edge_s);
+}
+
+__global__ void __launch_bounds__(256)
+heat_absdiff_max_f64(const double* __restrict__ a, const double* __restrict__ b, int row_lo, int row_hi, int ny, int64_t pitch,
+                     unsigned long long* __restrict__ resid)
+{
+    double m = 0.0;
+    const int64_t total = (int64_t)(row_hi - row_lo) * pitch;
+    for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
+        const int lr = (int)(k / pitch);
+        const int iy = (int)(k - (int64_t)lr * pitch);
+        if (iy < ny) {
+            const int64_t idx = k + (int64_t)row_lo * pitch;
+            m = fmax(m, fabs(__dsub_rn(a[idx], b[idx])));
+        }
+    }
+    block_max_to_global64(m, resid);
 }
 
 // ------------------------------------------------------------------ residual of two buffers

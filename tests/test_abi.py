@@ -34,7 +34,8 @@ def test_params_default_is_the_reference_default(ph):
     assert p.cx == np.float32(0.1) and p.cy == np.float32(0.1)  # struct Parms, M:29-32
     assert p.conv_every == 0 and p.conv_eps == np.float32(1e-3)
     assert p.nranks == 1 and p.temporal_block == 1
-    assert C.sizeof(ph.HeatParams) == 16 * 4
+    assert p.grid_type == ph.GRID_F32  # the reference's `float u` (M:46)
+    assert C.sizeof(ph.HeatParams) == 17 * 4
 
 
 def test_host_inidat_and_prtdat_match_reference(ph, golden, tmp_path):
