@@ -82,11 +82,14 @@ int heat_device_count(void);
 
 /* Environment variables read when a handle is created (tuning and debugging; defaults are the measured
  * best): HEAT_ROWS_PER_TILE (K1/K2 tile height, 8), HEAT_ROWS_PER_TILE_TB (K4 tile height, by row length),
- * HEAT_SERPENTINE (alternate sweep direction, 1), HEAT_GRAPHS (CUDA graphs of 16 passes, 1),
- * HEAT_RESIDENT (field resident in shared memory for grids that fit, 1), HEAT_RESIDENT_G (updates per
- * neighbour exchange of that kernel, 6), HEAT_TIMING (heat_solve prints its phases to stderr, 0),
+ * HEAT_K1_VARIANT (vec = register-streaming K1, bulk = shared-memory staged K1b, auto = bulk for rows of
+ * 16384 floats and more; default auto), HEAT_SERPENTINE (alternate sweep direction, 1), HEAT_GRAPHS (CUDA
+ * graphs of 16 passes, 1), HEAT_RESIDENT (field resident in shared memory for grids that fit, 1),
+ * HEAT_RESIDENT_G (updates per neighbour exchange of that kernel, 6), HEAT_TIMING (heat_solve prints its
+ * phases to stderr, 0), HEAT_SOLVE_STREAMED / HEAT_SOLVE_BAND_ROWS (heat_solve's overlapped upload, see
+ * there), HEAT_PROFILE_WAIT (count the edge CTAs' flag waits, see heat_debug_wait_stats, 0),
  * HEAT_COLS_FIRST (2-D blocks across processes: M > 0 hands the column-edge CTAs out first, M tile rows
- * each; 0 = grid order, the default -- bit-identical either way, slower on 2 GPUs, kept for the 2x4 study). */
+ * each; 0 = grid order, the default -- bit-identical either way and not faster in any layout measured). */
 
 /* ---- the reference's helpers, same arguments (M:315-341, C:274-300) ------------------ */
 /* inidat: u[ix*ny+iy] = (float)(ix*(nx-ix-1)*iy*(ny-iy-1)) in wrapping int32 (M:320). */
@@ -228,8 +231,8 @@ int heat_connect_local(heat_handle *h, heat_handle *north, heat_handle *south);
 int heat_group_run(heat_handle **strips, int n, int steps, int *updates_done, int *converged);
 /* 2-D blocks -- the reference's own cartesian topology (MPI_Cart_create, M:51-69; col_type halos,
  * M:82-84,139-155): block (rank, rank_y) of nranks x nranks_y also has a west and an east neighbour and
- * keeps one ghost column towards each; its first/last owned column is stored into the neighbour's ghost
- * column by the update kernel (one float per row).  temporal_block must be 1.  Inside one NVSwitch box row
+ * keeps one ghost column towards each, as a dense array of one float per local row beside the field; its
+ * first/last owned column is stored into the neighbour's array by the update kernel.  temporal_block must be 1.  Inside one NVSwitch box row
  * strips are the better choice (contiguous halos); blocks are for what comes after it. */
 int heat_connect_local2d(heat_handle *h, heat_handle *north, heat_handle *south, heat_handle *west, heat_handle *east);
 int heat_ipc_connect2d(heat_handle *h, const void *north_blob, const void *south_blob, const void *west_blob,
