@@ -515,7 +515,10 @@ static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, fl
     // K1b, the shared-memory staged variant: measured faster than the register-streaming kernel where rows are long
     // (16384 floats and more), slower below; "auto" picks by row length.  Row strips and the residual are supported,
     // column blocks are not.
-    const bool bulk = h->p.nranks_y == 1 && (h->k1_variant == 1 || (h->k1_variant == 2 && h->pitch >= BULK_MIN_PITCH));
+    // (MPI_F64MIX: measured slower staged, 680 vs 732 GLUP/s at 16384^2 -- its warps are busy converting, and the
+    // staged form has fewer loads in flight per warp -- so "auto" keeps that mode on K1)
+    const bool bulk = h->p.nranks_y == 1 &&
+                      (h->k1_variant == 1 || (h->k1_variant == 2 && h->pitch >= BULK_MIN_PITCH && ARITH != HEAT_ARITH_F64MIX));
     if (bulk) {
         constexpr int ROWS = HEAT_BULK_ROWS;
         if (h->ghost <= ROWS && (rows + ROWS - 1) / ROWS <= 65535) {

@@ -133,8 +133,8 @@ __device__ __forceinline__ float4 upd4_f64mix(const float4& c, const float4& n, 
 // four E+W sums stay scalar (their operands straddle the pairs): 16 floating-point instructions per float4
 // instead of 28.  Measured (round 2, one B200): nothing for K1 (852 vs 852 GLUP/s at 8192^2, 848 vs 851 at
 // 65536^2: the kernel waits for HBM, not for issue slots), but K4, which is FP32-issue-bound, gains: T=4 at
-// 32768^2 2620 -> 2670 GLUP/s (F32_FMA) and 2345 -> 2666 (F32_NOFMA, whose unfused multiplies and adds pack
-// best), 8192^2 2159 -> 2224.  So packed is the default in K4 (HEAT_PACKED_K4) and off in K1 (HEAT_PACKED_K1).
+// 32768^2 2620 -> 2670 GLUP/s, 8192^2 2159 -> 2224 (F32_FMA).  So packed is the default in K4 (HEAT_PACKED_K4)
+// and off in K1 (HEAT_PACKED_K1); F32_FMA only (see upd_quad).
 #ifndef HEAT_PACKED_K1
 #define HEAT_PACKED_K1 0
 #endif
@@ -207,7 +207,9 @@ __device__ __forceinline__ float4 upd_quad(const float4& c, const float4& n, con
 {
     if constexpr (ARITH == HEAT_ARITH_F64MIX && HEAT_F64_WIDEN_INT > 0) {
         return upd4_f64mix<HEAT_F64_WIDEN_INT>(c, n, s, wl, er, cx, cy);
-    } else if constexpr (ARITH != HEAT_ARITH_F64MIX && PACKED) {
+    } else if constexpr (ARITH == HEAT_ARITH_F32_FMA && PACKED) {
+        // F32_FMA only: ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 (it never fuses the scalar .rn forms),
+        // which would turn F32_NOFMA into F32_FMA -- caught by the parity tests, so F32_NOFMA stays scalar
         return upd4_packed<ARITH>(c, n, s, wl, er, cx, cy);
     } else {
         float4 o;
