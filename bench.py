@@ -590,6 +590,50 @@ def run_one(ctx, api, wl, arith, args):
             solver.close()
 
 
+def leg_3d(ctx, api, n, arith, args, peak):
+    """the 7-point update on an n^3 float grid, measured like every other leg; parity = three
+    slabs of planes against the oracle's 3-D mode (unpinned: the reference is 2-D only)."""
+    import numpy as np
+    from oracle import pyoracle as O
+    torch = ctx.torch
+    with api.HeatSolver(n, n, nz=n, device=ctx.local_rank, arith=arith) as s:
+        s.set_stream(ctx.stream.cuda_stream)
+        s.init_inidat()
+        K = args.steps
+        m = measure(ctx, s.enqueue, s.sync, K, max(args.warmup, 3), reps=args.reps or None, launch_count=s.launch_count)
+        ms = m["median_ms"]
+        lups = (n - 2) ** 3
+        value = lups * K / (ms * 1e-3) / 1e9
+        s.init_inidat()
+        U = 8
+        s.enqueue(U)
+        s.sync()
+        ptr, pitch, nloc, lo = s.device_view(0)
+        nbad = npts = 0
+        for x0 in (0, n // 2, n - 16):
+            got = device_window(torch, ptr, pitch, x0, x0 + 16, 0, n * n, ctx.local_rank).reshape(16, n, n)
+            a, b = max(0, x0 - U), min(n, x0 + 16 + U)
+            ix = np.arange(a, b, dtype=np.uint32)[:, None, None]
+            iy = np.arange(n, dtype=np.uint32)[None, :, None]
+            iz = np.arange(n, dtype=np.uint32)[None, None, :]
+            one, nn = np.uint32(1), np.uint32(n)
+            ini = (ix * (nn - ix - one) * iy * (nn - iy - one) * iz * (nn - iz - one)).view(np.int32).astype(np.float32)
+            want = O.solve3d(ini, U, arith=arith)[0][x0 - a:x0 - a + 16]
+            nbad += int((got.view(np.uint32) != want.view(np.uint32)).sum())
+            npts += got.size
+    achieved = BYTES_PER_LUP * lups / (ms / K * 1e-3) / 1e9
+    return {"value": value, "unit": "GLUP/s", "ms_per_step": ms / K, "steps": K, "reps": m["reps"],
+            "rep_ms": {"best": m["best_ms"], "median": m["median_ms"], "worst": m["worst_ms"]},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "kernel": "heat_step_3d", "traffic": ncu_traffic(f"heat_step_3d@{n}x{n}x{n}"),
+                         "algorithmic_bytes_per_launch": BYTES_PER_LUP * lups},
+            "clocks": m["clocks"], "gpu_launches": m["launches"],
+            "parity": {"windows": 3, "points": npts, "mismatches": nbad, "bit_exact": nbad == 0, "updates": U,
+                       "against": "oracle.solve3d on three 16-plane slabs + margin (unpinned: the reference is 2-D only)"},
+            "workload": f"{n}x{n}x{n} float32 3-D inidat field, 7-point update, no convergence check", "arith": api.ARITH_NAMES[arith],
+            "note": "SURVEY 8(f) rank 4: 3-D 7-point variant, 8 B per point-update"}
+
+
 def e2e_single(ctx, api, wl, arith, K):
     """heat_solve() on pinned HOST memory: H2D + K updates + D2H inside the timed region, wall clock, median of 3."""
     import ctypes as C
@@ -697,6 +741,11 @@ def run_ours(args, wl, rank, world, local_rank):
     clocks = ClockSampler(local_rank).start()  # NVML initialised here, long before any timed region
     ctx = Ctx(torch, dist, rank, world, local_rank, stream, clocks)
     peak, _ = measured_peak()
+    if args.only_3d:
+        r = leg_3d(ctx, api, args.only_3d, arith, args, peak)
+        clocks.stop()
+        print(json.dumps(r), flush=True)
+        return 0 if r["parity"]["bit_exact"] else 3
     try:
         main = run_one(ctx, api, wl, arith, args)
 
@@ -742,6 +791,7 @@ def run_ours(args, wl, rank, world, local_rank):
                     leg("mpi_f64mix_c2_8192", "c2", api.MPI_F64MIX, "8192x8192 in the MPI program's arithmetic")
             leg("f64_grid_16384", "g16k_f64", arith, "SURVEY 8(f) rank 4: the same update on a DOUBLE-precision grid (16 B per point-update, "
                 "so the HBM roofline is half as many LUP/s); parity unpinned -- the reference has no double build")
+            also["grid3d_640"] = leg_3d(ctx, api, 640, arith, args, peak)
             also["reference_cuda"] = reference_cuda_leg(peak)
 
         if world > 1 and not args.no_also and args.cols == 1 and wl["name"] != "weak32k":
@@ -798,6 +848,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-also", action="store_true", help="skip the other 1-GPU configurations")
     ap.add_argument("--k3-profile", action="store_true", help="N>1: per-rank edge-CTA flag-wait time and NVLink bytes per pass")
+    ap.add_argument("--only-3d", type=int, default=0, help="measure only the 3-D leg on an N^3 grid (kernel tuning)")
     ap.add_argument("--no-parity", action="store_true", help="skip the bit-exact window check after the timed region")
     args = ap.parse_args()
 

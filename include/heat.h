@@ -46,6 +46,13 @@ extern "C" {
 #define HEAT_GRID_F32    0
 #define HEAT_GRID_F64    1
 
+/* 3-D grids (the reference is 2-D only): nz > 1 makes the grid nx*ny*nz, dense, iz fastest,
+ * and the update the 7-point one, new = u + cx*((X+ + X-) - 2u) + cy*((Y+ + Y-) - 2u) + cz*((Z+ + Z-) - 2u),
+ * evaluated left to right in the arithmetic `arith` names (F32_FMA: three fused multiply-adds); all six faces
+ * are the ring.  nz must be a multiple of 4; one GPU, float, single updates (nranks 1, nranks_y 1,
+ * temporal_block 1).  heat_solve, heat_upload, heat_download, heat_init_inidat, heat_run and the convergence
+ * check work as in 2-D on the nx*ny*nz array. */
+
 /* How many updates `steps` means, and when convergence is checked. */
 #define HEAT_STEPS_CUDA  0 /* `steps` updates                 (C:204  i <  STEPS) */
 #define HEAT_STEPS_MPI   1 /* `steps`+1 updates               (M:159  it <= STEPS) */
@@ -68,6 +75,8 @@ typedef struct heat_params {
     int   rank, nranks;    /* row-strip decomposition: this handle owns strip `rank`   */
     int   rank_y, nranks_y;/* column blocks on top of that (2-D blocks, M:51-75); 0, 1 = row strips only */
     int   grid_type;       /* HEAT_GRID_F32 (the reference's `float u`, M:46, C:170) | HEAT_GRID_F64       */
+    int   nz;              /* 0 or 1: the reference's 2-D grid; > 1: 3-D grid u[ix][iy][iz], iz fastest    */
+    float cz;              /* coefficient of the iz +-1 term of the 3-D update; 0.1f                       */
 } heat_params;
 
 typedef struct heat_handle heat_handle; /* opaque: owns device buffers, stream, graphs */
@@ -95,6 +104,8 @@ int heat_device_count(void);
 /* inidat: u[ix*ny+iy] = (float)(ix*(nx-ix-1)*iy*(ny-iy-1)) in wrapping int32 (M:320). */
 int heat_inidat(int nx, int ny, float *u);
 int heat_inidat_f64(int nx, int ny, double *u); /* same int product, same wrap, stored as double */
+/* The 3-D twin: (float)(ix*(nx-ix-1)*iy*(ny-iy-1)*iz*(nz-iz-1)) in the same wrapping int arithmetic. */
+int heat_inidat3d(int nx, int ny, int nz, float *u);
 /* prtdat: "%6.1f" text, iy descending outer, ix ascending inner (M:326-341). */
 int heat_prtdat(int nx, int ny, const float *u, const char *fnam);
 /* Binary twin of prtdat: 16-byte header {"HEATB200", int32 nx, int32 ny} + nx*ny floats. */

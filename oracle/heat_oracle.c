@@ -216,3 +216,80 @@ int oracle_solve_f64(int fused, int nx, int ny, int steps, float cx, float cy, i
     if (converged) *converged = conv;
     return 0;
 }
+
+/* ---------------------------------------------------------------------------------------------------------
+ * 3-D, 7-point.  PARITY UNPINNED: the reference is 2-D only.  Its expression (M:168-174 /
+ * C:155-161) with a third neighbour pair, evaluated left to right: u + cx*((X+ + X-) - 2u) + cy*((Y+ + Y-) - 2u)
+ * + cz*((Z+ + Z-) - 2u), in the same three arithmetics.  u[ix][iy][iz], iz fastest; all six faces are the ring. */
+void oracle_inidat3d(int nx, int ny, int nz, float *u)
+{
+    for (int ix = 0; ix < nx; ix++)
+        for (int iy = 0; iy < ny; iy++) {
+            uint32_t a = (uint32_t)ix * (uint32_t)(nx - ix - 1) * (uint32_t)iy * (uint32_t)(ny - iy - 1);
+            for (int iz = 0; iz < nz; iz++)
+                u[((int64_t)ix * ny + iy) * nz + iz] = (float)(int32_t)(a * (uint32_t)iz * (uint32_t)(nz - iz - 1));
+        }
+}
+
+static inline float upd3_oracle(int arith, float c, float xs, float ys, float zs, float cx, float cy, float cz)
+{
+    if (arith == ORACLE_F32_FMA)
+        return fmaf(cz, zs - 2.0f * c, fmaf(cy, ys - 2.0f * c, fmaf(cx, xs - 2.0f * c, c)));
+    if (arith == ORACLE_F32_NOFMA) {
+        float a = cx * (xs - 2.0f * c);
+        float r = c + a;
+        float b = cy * (ys - 2.0f * c);
+        r = r + b;
+        float d = cz * (zs - 2.0f * c);
+        return r + d;
+    }
+    double cd = (double)c;
+    double r = cd + (double)cx * ((double)xs - 2.0 * cd);
+    r = r + (double)cy * ((double)ys - 2.0 * cd);
+    r = r + (double)cz * ((double)zs - 2.0 * cd);
+    return (float)r;
+}
+
+void oracle_step3d(int arith, int nx, int ny, int nz, float cx, float cy, float cz, const float *in, float *out)
+{
+    const int64_t sx = (int64_t)ny * nz, sy = nz;
+#pragma omp parallel for schedule(static)
+    for (int i = 1; i < nx - 1; i++)
+        for (int j = 1; j < ny - 1; j++) {
+            const float *c = in + i * sx + j * sy;
+            float *o = out + i * sx + j * sy;
+            for (int k = 1; k < nz - 1; k++) {
+                float xs = c[k + sx] + c[k - sx];
+                float ys = c[k + sy] + c[k - sy];
+                float zs = c[k + 1] + c[k - 1];
+                o[k] = upd3_oracle(arith, c[k], xs, ys, zs, cx, cy, cz);
+            }
+        }
+}
+
+int oracle_solve3d(int arith, int nx, int ny, int nz, int steps, float cx, float cy, float cz, int conv_every, float conv_eps,
+                   int conv_phase, int step_convention, float *grid, float *work, int *updates_done, int *converged)
+{
+    if (nx < 1 || ny < 1 || nz < 1 || steps < 0 || !grid || !work) return -1;
+    const int64_t n = (int64_t)nx * ny * nz;
+    memcpy(work, grid, (size_t)n * sizeof(float));
+    float *buf[2] = {grid, work};
+    int old = 0, done = 0, conv = 0;
+    const int total = steps + (step_convention ? 1 : 0);
+    for (int it = 0; it < total; it++) {
+        oracle_step3d(arith, nx, ny, nz, cx, cy, cz, buf[old], buf[1 - old]);
+        old = 1 - old;
+        done = it + 1;
+        if (conv_every > 0) {
+            int check = conv_phase ? (it % conv_every == 0) : ((it + 1) % conv_every == 0);
+            if (check && oracle_max_abs_diff(n, buf[0], buf[1]) < conv_eps) {
+                conv = 1;
+                break;
+            }
+        }
+    }
+    if (old == 1) memcpy(grid, work, (size_t)n * sizeof(float));
+    if (updates_done) *updates_done = done;
+    if (converged) *converged = conv;
+    return 0;
+}

@@ -60,6 +60,12 @@ void oracle_step_f64(int fused, int nx, int ny, float cx, float cy, const double
 int oracle_solve_f64(int fused, int nx, int ny, int steps, float cx, float cy, int conv_every, float conv_eps,
                      int conv_phase, int step_convention, double *grid, double *work, int *updates_done, int *converged);
 
+/* 3-D 7-point grids: PARITY UNPINNED (the reference is 2-D only; see heat_oracle.c). */
+void oracle_inidat3d(int nx, int ny, int nz, float *u);
+void oracle_step3d(int arith, int nx, int ny, int nz, float cx, float cy, float cz, const float *in, float *out);
+int oracle_solve3d(int arith, int nx, int ny, int nz, int steps, float cx, float cy, float cz, int conv_every, float conv_eps,
+                   int conv_phase, int step_convention, float *grid, float *work, int *updates_done, int *converged);
+
 /* number of OpenMP threads the oracle will use (1 when built without OpenMP) */
 int oracle_threads(void);
 

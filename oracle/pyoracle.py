@@ -50,6 +50,11 @@ def lib():
                                                    _fp, _fp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.oracle_solve.restype = C.c_int
         L.oracle_threads.restype = C.c_int
+        L.oracle_inidat3d.argtypes = [C.c_int, C.c_int, C.c_int, _fp]
+        L.oracle_inidat3d.restype = None
+        L.oracle_solve3d.argtypes = [C.c_int] * 5 + [C.c_float] * 3 + [C.c_int, C.c_float, C.c_int, C.c_int, _fp, _fp,
+                                                                     C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.oracle_solve3d.restype = C.c_int
         _dp = C.POINTER(C.c_double)
         L.oracle_inidat_f64.argtypes = [C.c_int, C.c_int, _dp]
         L.oracle_inidat_f64.restype = None
@@ -107,6 +112,26 @@ def solve(grid, steps, arith=F32_NOFMA, cx=0.1, cy=0.1, conv_every=0, conv_eps=1
 
 def threads():
     return lib().oracle_threads()
+
+
+# 3-D 7-point grids: PARITY UNPINNED (the reference is 2-D only, see heat_oracle.c)
+def inidat3d(nx, ny, nz):
+    u = np.empty((nx, ny, nz), np.float32)
+    lib().oracle_inidat3d(nx, ny, nz, _p(u))
+    return u
+
+
+def solve3d(grid, steps, arith=F32_NOFMA, cx=0.1, cy=0.1, cz=0.1, conv_every=0, conv_eps=1e-3, conv_phase=0, step_convention=0):
+    """Returns (final grid, updates_done, converged) for a float32 grid of shape (nx, ny, nz)."""
+    g = np.array(grid, np.float32, order="C", copy=True)
+    nx, ny, nz = g.shape
+    work = np.empty_like(g)
+    done, conv = C.c_int(0), C.c_int(0)
+    rc = lib().oracle_solve3d(arith, nx, ny, nz, steps, cx, cy, cz, conv_every, np.float32(conv_eps), conv_phase,
+                              step_convention, _p(g), _p(work), C.byref(done), C.byref(conv))
+    if rc:
+        raise ValueError("oracle_solve3d: bad arguments")
+    return g, done.value, bool(conv.value)
 
 
 # double-precision grids: PARITY UNPINNED (no reference build exists for them, see heat_oracle.c)

@@ -41,7 +41,7 @@ class HeatParams(C.Structure):
                 ("conv_every", C.c_int), ("conv_eps", C.c_float), ("conv_phase", C.c_int),
                 ("step_convention", C.c_int), ("arith", C.c_int), ("temporal_block", C.c_int),
                 ("device", C.c_int), ("rank", C.c_int), ("nranks", C.c_int), ("rank_y", C.c_int), ("nranks_y", C.c_int),
-                ("grid_type", C.c_int)]
+                ("grid_type", C.c_int), ("nz", C.c_int), ("cz", C.c_float)]
 
 
 ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.POINTER(C.c_float), C.c_void_p)
@@ -63,6 +63,7 @@ SIGNATURES = {
     "heat_solve": (C.c_int, [C.POINTER(HeatParams), _fp, _ip, _ip]),
     "heat_solve_f64": (C.c_int, [C.POINTER(HeatParams), _dp, _ip, _ip]),
     "heat_inidat_f64": (C.c_int, [C.c_int, C.c_int, _dp]),
+    "heat_inidat3d": (C.c_int, [C.c_int, C.c_int, C.c_int, _fp]),
     "heat_upload_f64": (C.c_int, [_H, _dp]),
     "heat_download_f64": (C.c_int, [_H, _dp]),
     "heat_solve_gpus": (C.c_int, [C.POINTER(HeatParams), C.c_int, _fp, _ip, _ip]),
@@ -156,6 +157,12 @@ def inidat_f64(nx, ny):
     return u
 
 
+def inidat3d(nx, ny, nz):
+    u = np.empty((nx, ny, nz), np.float32)
+    _check(load().heat_inidat3d(nx, ny, nz, u.ctypes.data_as(_fp)))
+    return u
+
+
 def prtdat(u, fnam):
     u, p = _f32(u)
     _check(load().heat_prtdat(u.shape[0], u.shape[1], p, str(fnam).encode()))
@@ -185,6 +192,8 @@ def solve(grid, steps, **params):
     grid_type=GRID_F64 takes / returns float64 through heat_solve_f64()."""
     f64 = params.get("grid_type", GRID_F32) == GRID_F64
     g = np.array(grid, dtype=np.float64 if f64 else np.float32, order="C", copy=True)
+    if g.ndim == 3:  # 3-D grid u[ix][iy][iz]
+        params = dict(params, nz=g.shape[2])
     p = default_params(nx=g.shape[0], ny=g.shape[1], steps=steps, **params)
     done, conv = C.c_int(0), C.c_int(0)
     if f64:
@@ -211,6 +220,12 @@ class HeatSolver:
         self._h = _H()
         self._cb = None
         _check(load().heat_create(C.byref(self.params), C.byref(self._h)))
+
+    @property
+    def shape(self):
+        """Shape of the full grid: (nx, ny), or (nx, ny, nz) for a 3-D grid."""
+        p = self.params
+        return (p.nx, p.ny, p.nz) if p.nz > 1 else (p.nx, p.ny)
 
     # -- lifetime
     def close(self):
@@ -239,8 +254,8 @@ class HeatSolver:
             g = np.ascontiguousarray(full_grid, dtype=np.float64)
         else:
             g, p = _f32(full_grid)
-        if g.shape != (self.params.nx, self.params.ny):
-            raise ValueError(f"grid shape {g.shape} != ({self.params.nx}, {self.params.ny})")
+        if g.shape != self.shape:
+            raise ValueError(f"grid shape {g.shape} != {self.shape}")
         if self.params.grid_type == GRID_F64:
             _check(load().heat_upload_f64(self._h, g.ctypes.data_as(_dp)))
         else:
@@ -255,7 +270,7 @@ class HeatSolver:
     def download(self, out=None):
         f64 = self.params.grid_type == GRID_F64
         if out is None:
-            out = np.zeros((self.params.nx, self.params.ny), np.float64 if f64 else np.float32)
+            out = np.zeros(self.shape, np.float64 if f64 else np.float32)
         assert out.dtype == (np.float64 if f64 else np.float32) and out.flags.c_contiguous
         if f64:
             _check(load().heat_download_f64(self._h, out.ctypes.data_as(_dp)))

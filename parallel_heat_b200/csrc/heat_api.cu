@@ -66,6 +66,8 @@ extern "C" int heat_params_default(heat_params* p)
     p->rank_y = 0;
     p->nranks_y = 1;
     p->grid_type = HEAT_GRID_F32;
+    p->nz = 1;
+    p->cz = 0.1f;
     return HEAT_OK;
 }
 
@@ -89,6 +91,18 @@ extern "C" int heat_inidat_f64(int nx, int ny, double* u)
         double* row = u + (size_t)ix * ny;
         for (int iy = 0; iy < ny; iy++) row[iy] = (double)(int32_t)(a * (uint32_t)iy * (uint32_t)(ny - iy - 1));
     }
+    return HEAT_OK;
+}
+
+extern "C" int heat_inidat3d(int nx, int ny, int nz, float* u)
+{
+    if (nx < 1 || ny < 1 || nz < 1 || !u) return fail(HEAT_E_INVALID, "heat_inidat3d: bad arguments");
+    for (int ix = 0; ix < nx; ix++)
+        for (int iy = 0; iy < ny; iy++) {
+            const uint32_t a = (uint32_t)ix * (uint32_t)(nx - ix - 1) * (uint32_t)iy * (uint32_t)(ny - iy - 1);
+            float* row = u + ((size_t)ix * ny + iy) * nz;
+            for (int iz = 0; iz < nz; iz++) row[iz] = (float)(int32_t)(a * (uint32_t)iz * (uint32_t)(nz - iz - 1));
+        }
     return HEAT_OK;
 }
 
@@ -222,6 +236,7 @@ struct heat_handle {
     int col0 = 0, cols_own = 0; // owned global columns [col0, col0+cols_own) (2-D blocks; else all)
     int lo_c = 0, nyloc = 0;    // local array = global columns [lo_c, lo_c+nyloc): + one ghost column per neighbour
     int64_t pitch = 0;          // row pitch in FLOATS (4-byte units) whatever the element type: buf[k] + r*pitch is row r
+    int nz = 1, ny3 = 0;        // 3-D grids: nz > 1 and ny3 = the caller's ny; a handle row is then one ix-plane of ny3*nz floats (p.ny)
     int es = 1;                 // floats per element: 1 = float grid, 2 = double grid (HEAT_GRID_F64)
     float* buf[2] = {nullptr, nullptr};
     int cur = 0;                // index of the newest buffer
@@ -313,6 +328,13 @@ static int validate(const heat_params* p)
     if (p->grid_type != HEAT_GRID_F32 && p->grid_type != HEAT_GRID_F64) return fail(HEAT_E_INVALID, "params: grid_type=%d", p->grid_type);
     if (p->grid_type == HEAT_GRID_F64 && (p->temporal_block != 1 || p->nranks_y != 1))
         return fail(HEAT_E_INVALID, "params: double-precision grids run single updates on row strips (temporal_block 1, nranks_y 1)");
+    if (p->nz < 0) return fail(HEAT_E_INVALID, "params: nz=%d", p->nz);
+    if (p->nz > 1) {
+        if (p->nz % 4 || p->nz < 4) return fail(HEAT_E_INVALID, "params: nz=%d (3-D grids need nz a multiple of 4)", p->nz);
+        if ((long long)p->ny * p->nz > 0x7fffffffLL) return fail(HEAT_E_INVALID, "params: ny*nz=%lld does not fit an int", (long long)p->ny * p->nz);
+        if (p->nranks != 1 || p->nranks_y != 1 || p->temporal_block != 1 || p->grid_type != HEAT_GRID_F32)
+            return fail(HEAT_E_INVALID, "params: 3-D grids run single float updates on one GPU (nranks 1, nranks_y 1, temporal_block 1)");
+    }
     if (p->conv_phase != HEAT_PHASE_MPI && p->conv_phase != HEAT_PHASE_CUDA)
         return fail(HEAT_E_INVALID, "params: conv_phase=%d", p->conv_phase);
     if (p->step_convention != HEAT_STEPS_CUDA && p->step_convention != HEAT_STEPS_MPI)
@@ -354,12 +376,16 @@ extern "C" int heat_destroy(heat_handle* h)
     return HEAT_OK;
 }
 
-extern "C" int heat_create(const heat_params* p, heat_handle** out)
+extern "C" int heat_create(const heat_params* p_in, heat_handle** out)
 {
     if (!out) return fail(HEAT_E_INVALID, "heat_create: null out");
     *out = nullptr;
-    int rc = validate(p);
+    int rc = validate(p_in);
     if (rc) return rc;
+    // 3-D grids: everything below (buffers, copies, streaming, residual pass) sees nx rows of ny*nz floats
+    heat_params folded = *p_in;
+    if (folded.nz > 1) folded.ny = p_in->ny * p_in->nz;
+    const heat_params* p = &folded;
     int ndev = 0;
     CK(cudaGetDeviceCount(&ndev));
     if (p->device < 0 || p->device >= ndev) return fail(HEAT_E_INVALID, "heat_create: device %d of %d", p->device, ndev);
@@ -368,6 +394,7 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     heat_handle* h = new (std::nothrow) heat_handle();
     if (!h) return fail(HEAT_E_NOMEM, "heat_create: out of host memory");
     h->p = *p;
+    if (p_in->nz > 1) h->nz = p_in->nz, h->ny3 = p_in->ny;
     heat_strip_rows(p->nx, p->nranks, p->rank, &h->row0, &h->rows_own);
     // local array: owned rows plus one ghost row towards each existing neighbour
     // (T ghost rows when T updates are fused per pass: they are refreshed once per pass)
@@ -451,7 +478,7 @@ extern "C" int heat_create(const heat_params* p, heat_handle** out)
     h->use_graphs = env_int("HEAT_GRAPHS", 1) != 0;
     h->use_resident = env_int("HEAT_RESIDENT", 1) != 0;
 #endif
-    if (h->es == 2) h->use_resident = false; // K5 keeps a float field in shared memory
+    if (h->es == 2 || h->nz > 1) h->use_resident = false; // K5 keeps a 2-D float field in shared memory
     *out = h;
     return HEAT_OK;
 }
@@ -649,9 +676,41 @@ static cudaError_t launch_step_f64_t(heat_handle* h, const float* in, float* out
     return cudaGetLastError();
 }
 
+// 3-D 7-point update: planes [upd_lo, upd_hi) of the handle's rows
+template <int ARITH, bool RESID>
+static cudaError_t launch_step_3d_t(heat_handle* h, const float* in, float* out)
+{
+    const int planes = h->upd_hi - h->upd_lo, ny = h->ny3, nz = h->nz;
+    if (planes < 1 || ny < 3 || nz < 4) return cudaSuccess;
+    constexpr int TY = 4, WARPS = 4;
+    // plane tiles: enough CTAs for a few waves, tiles no shorter than 8 planes (two planes of halo per tile)
+    const long long ctas_xy = (long long)((nz / 4 + 31) / 32) * ((ny - 2 + TY * WARPS - 1) / (TY * WARPS));
+    int ppt = planes;
+    while (ppt > 8 && ctas_xy * ((planes + ppt - 1) / ppt) < 4LL * h->sm_count) ppt = (ppt + 1) / 2;
+    if ((planes + ppt - 1) / ppt > 65535) ppt = (planes + 65534) / 65535;
+    dim3 grid((unsigned)((nz / 4 + 31) / 32), (unsigned)((ny - 2 + TY * WARPS - 1) / (TY * WARPS)), (unsigned)((planes + ppt - 1) / ppt));
+    heat_step_3d<ARITH, RESID, TY, WARPS><<<grid, 32 * WARPS, 0, h->stream>>>(in, out, h->upd_lo, h->upd_hi, ny, nz, h->pitch, ppt, h->p.cx,
+                                                                            h->p.cy, h->p.cz, h->d_resid);
+    h->launches++;
+    return cudaGetLastError();
+}
+
+static cudaError_t launch_step_3d(heat_handle* h, bool resid, const float* in, float* out)
+{
+    switch (h->p.arith * 2 + (resid ? 1 : 0)) {
+    case 0: return launch_step_3d_t<HEAT_ARITH_F32_FMA, false>(h, in, out);
+    case 1: return launch_step_3d_t<HEAT_ARITH_F32_FMA, true>(h, in, out);
+    case 2: return launch_step_3d_t<HEAT_ARITH_F32_NOFMA, false>(h, in, out);
+    case 3: return launch_step_3d_t<HEAT_ARITH_F32_NOFMA, true>(h, in, out);
+    case 4: return launch_step_3d_t<HEAT_ARITH_F64MIX, false>(h, in, out);
+    default: return launch_step_3d_t<HEAT_ARITH_F64MIX, true>(h, in, out);
+    }
+}
+
 static cudaError_t launch_step(heat_handle* h, bool resid, const float* in, float* out, float* peer_n, float* peer_s,
                                int reverse)
 {
+    if (h->nz > 1) return launch_step_3d(h, resid, in, out);
     if (h->es == 2) {
         const bool fma = h->p.arith == HEAT_F32_FMA;
         return fma ? (resid ? launch_step_f64_t<true, true>(h, in, out, peer_n, peer_s, reverse)
@@ -1263,7 +1322,9 @@ extern "C" int heat_init_inidat(heat_handle* h)
         int rc = quiesce_neighbours(h);
         if (rc) return rc;
     }
-    if (h->es == 2)
+    if (h->nz > 1)
+        heat_inidat3d_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(h->buf[0], h->buf[1], h->p.nx, h->ny3, h->nz, h->nloc, h->pitch);
+    else if (h->es == 2)
         heat_inidat_f64_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>((double*)h->buf[0], (double*)h->buf[1], h->p.nx, h->p.ny, h->lo,
                                                                        h->nloc, h->pitch / 2, h->lo_c, h->nyloc);
     else

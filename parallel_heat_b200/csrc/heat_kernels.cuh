@@ -1253,6 +1253,125 @@ heat_absdiff_max_f64(const double* __restrict__ a, const double* __restrict__ b,
     block_max_to_global64(m, resid);
 }
 
+// ------------------------------------------------------------------ 3-D, 7-point
+// The reference is 2-D only; this is its update with a third axis: u[ix][iy][iz], iz fastest,
+//   new = u + cx*((X+ + X-) - 2u) + cy*((Y+ + Y-) - 2u) + cz*((Z+ + Z-) - 2u),   evaluated left to right,
+// in the same three arithmetics (F32_FMA: one more fused multiply-add on the chain; MPI_F64MIX: float
+// neighbour sums, the rest in double).  All six faces are the ring.  A "row" of the handle is one ix-plane
+// (ny*nz floats), so upload, download, the streamed one-shot and the residual pass are the 2-D ones.
+// Register-blocked column streaming, one dimension up: lanes run along iz (one float4 each), a thread owns TY
+// consecutive iy rows of its four columns and streams along ix with the previous, current and next plane of
+// those rows in registers.  Y neighbours inside the thread's rows are its own registers, the two rows beyond
+// come with the plane (TY+2 loads for TY outputs, the extra ones L1/L2 hits of the neighbouring warps), Z
+// neighbours are shuffles (across the warp edge: one 4-byte load).  No shared memory.
+template <int ARITH>
+__device__ __forceinline__ float upd3(float c, float xs, float ys, float zs, float cx, float cy, float cz)
+{
+    // xs, ys, zs: the three float neighbour sums
+    if constexpr (ARITH == HEAT_ARITH_F32_FMA) {
+        const float c2 = __fadd_rn(c, c);
+        return __fmaf_rn(cz, __fsub_rn(zs, c2), __fmaf_rn(cy, __fsub_rn(ys, c2), __fmaf_rn(cx, __fsub_rn(xs, c2), c)));
+    } else if constexpr (ARITH == HEAT_ARITH_F32_NOFMA) {
+        const float c2 = __fadd_rn(c, c);
+        float r = __fadd_rn(c, __fmul_rn(cx, __fsub_rn(xs, c2)));
+        r = __fadd_rn(r, __fmul_rn(cy, __fsub_rn(ys, c2)));
+        return __fadd_rn(r, __fmul_rn(cz, __fsub_rn(zs, c2)));
+    } else {
+        const double cd = (double)c, c2 = __dadd_rn(cd, cd);
+        double r = __dadd_rn(cd, __dmul_rn((double)cx, __dsub_rn((double)xs, c2)));
+        r = __dadd_rn(r, __dmul_rn((double)cy, __dsub_rn((double)ys, c2)));
+        r = __dadd_rn(r, __dmul_rn((double)cz, __dsub_rn((double)zs, c2)));
+        return __double2float_rn(r);
+    }
+}
+
+__global__ void heat_inidat3d_kernel(float* __restrict__ a, float* __restrict__ b, int nx, int ny, int nz, int nplanes, int64_t pitch)
+{
+    const int64_t total = (int64_t)nplanes * pitch, plane = (int64_t)ny * nz;
+    for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
+        const int ix = (int)(k / pitch);
+        const int64_t in_plane = k - (int64_t)ix * pitch;
+        float v = 0.0f;
+        if (in_plane < plane) {
+            const int iy = (int)(in_plane / nz), iz = (int)(in_plane - (int64_t)iy * nz);
+            // the 2-D product of M:320 with a third factor pair, in the same wrapping int arithmetic
+            uint32_t p = (uint32_t)ix * (uint32_t)(nx - ix - 1) * (uint32_t)iy * (uint32_t)(ny - iy - 1) * (uint32_t)iz *
+                         (uint32_t)(nz - iz - 1);
+            v = (float)(int32_t)p;
+        }
+        a[k] = v;
+        b[k] = v;
+    }
+}
+
+//   grid.x = ceil(nz/4 / 32), grid.y = ceil((ny-2) / (TY*WARPS)), grid.z = plane tiles; block = 32*WARPS
+//   planes [plane_lo, plane_hi) are updated (planes plane_lo-1 and plane_hi must exist)
+template <int ARITH, bool RESID, int TY, int WARPS>
+__global__ void __launch_bounds__(32 * WARPS)
+heat_step_3d(const float* __restrict__ in, float* __restrict__ out, int plane_lo, int plane_hi, int ny, int nz, int64_t pitch,
+             int planes_per_tile, float cx, float cy, float cz, unsigned* __restrict__ resid)
+{
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int col = ((int)blockIdx.x * 32 + lane) * 4;                    // my first iz
+    const int y0 = 1 + ((int)blockIdx.y * WARPS + warp) * TY;         // my first iy (interior rows start at 1)
+    const int x0 = plane_lo + (int)blockIdx.z * planes_per_tile, x1 = min(x0 + planes_per_tile, plane_hi);
+    float m = 0.0f;
+    const bool live = col < nz;
+    if (y0 < ny - 1 && col - lane * 4 < nz) { // else this warp has no row / no column to update (warp-uniform)
+        if (!live) col = nz - 4; // keep the lane in bounds for loads; it never stores
+        const bool kx = (col == 0), kw = (col + 3 == nz - 1); // ring columns iz = 0 and nz-1: copied through
+        const bool e0 = lane == 0 && col > 0, e31 = lane == 31 && col + 4 < nz;
+        // rows y0-1 .. y0+TY of a plane; rows past ny-1 are clamped (loaded, never used for a store)
+        int64_t roff[TY + 2];
+#pragma unroll
+        for (int k = 0; k < TY + 2; k++) roff[k] = (int64_t)min(y0 - 1 + k, ny - 1) * nz + col;
+        float4 n[TY], c[TY + 2], s[TY + 2];
+        const float* pn = in + (int64_t)(x0 - 1) * pitch;
+#pragma unroll
+        for (int k = 0; k < TY; k++) n[k] = ld4(pn + roff[k + 1]);
+#pragma unroll
+        for (int k = 0; k < TY + 2; k++) c[k] = ld4(pn + pitch + roff[k]);
+        for (int x = x0; x < x1; x++) {
+            const float* pc = in + (int64_t)x * pitch;
+            const float* ps = pc + pitch;
+#pragma unroll
+            for (int k = 0; k < TY + 2; k++) s[k] = ld4(ps + roff[k]);
+            float* q = out + (int64_t)x * pitch;
+#pragma unroll
+            for (int k = 1; k <= TY; k++) {
+                const int y = y0 - 1 + k;
+                float wl = __shfl_up_sync(FULL, c[k].w, 1);
+                float er = __shfl_down_sync(FULL, c[k].x, 1);
+                if (y < ny - 1) {
+                    if (e0) wl = ld1(pc + roff[k] - 1);
+                    if (e31) er = ld1(pc + roff[k] + 4);
+                    const float4 cc = c[k], up = c[k - 1], dn = c[k + 1], xm = n[k - 1], xp = s[k];
+                    float4 o;
+                    o.x = upd3<ARITH>(cc.x, __fadd_rn(xp.x, xm.x), __fadd_rn(dn.x, up.x), __fadd_rn(cc.y, wl), cx, cy, cz);
+                    o.y = upd3<ARITH>(cc.y, __fadd_rn(xp.y, xm.y), __fadd_rn(dn.y, up.y), __fadd_rn(cc.z, cc.x), cx, cy, cz);
+                    o.z = upd3<ARITH>(cc.z, __fadd_rn(xp.z, xm.z), __fadd_rn(dn.z, up.z), __fadd_rn(cc.w, cc.y), cx, cy, cz);
+                    o.w = upd3<ARITH>(cc.w, __fadd_rn(xp.w, xm.w), __fadd_rn(dn.w, up.w), __fadd_rn(er, cc.z), cx, cy, cz);
+                    if (kx) o.x = cc.x;
+                    if (kw) o.w = cc.w;
+                    if (live) st4(q + roff[k], o);
+                    if (RESID) {
+                        m = fmaxf(m, fabsf(__fsub_rn(cc.x, o.x)));
+                        m = fmaxf(m, fabsf(__fsub_rn(cc.y, o.y)));
+                        m = fmaxf(m, fabsf(__fsub_rn(cc.z, o.z)));
+                        m = fmaxf(m, fabsf(__fsub_rn(cc.w, o.w)));
+                    }
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < TY; k++) n[k] = c[k + 1];
+#pragma unroll
+            for (int k = 0; k < TY + 2; k++) c[k] = s[k];
+        }
+    }
+    if (RESID) block_max_to_global(live ? m : 0.0f, resid);
+}
+
 // ------------------------------------------------------------------ residual of two buffers
 // max |a-b| over the interior of a strip (heat_residual(): a separate pass, not on the hot path)
 __global__ void __launch_bounds__(256)

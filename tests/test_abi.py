@@ -35,7 +35,8 @@ def test_params_default_is_the_reference_default(ph):
     assert p.conv_every == 0 and p.conv_eps == np.float32(1e-3)
     assert p.nranks == 1 and p.temporal_block == 1
     assert p.grid_type == ph.GRID_F32  # the reference's `float u` (M:46)
-    assert C.sizeof(ph.HeatParams) == 17 * 4
+    assert p.nz == 1 and p.cz == np.float32(0.1)  # 2-D, like the reference
+    assert C.sizeof(ph.HeatParams) == 19 * 4
 
 
 def test_host_inidat_and_prtdat_match_reference(ph, golden, tmp_path):

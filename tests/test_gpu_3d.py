@@ -1,0 +1,84 @@
+"""3-D 7-point grids: libheat_b200.so against the oracle's 3-D mode.
+
+PARITY UNPINNED: the reference is 2-D only, so the oracle mode these tests compare with is its expression with a
+third neighbour pair (checked against an independent numpy statement in tests/test_oracle.py), not a recording
+of the reference.  Checked here: bit-equality with that restatement in all three arithmetics, the ring, the
+convergence check, and that tiling and the streamed one-shot path do not change the bits."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def same_bits(a, b, what=""):
+    a, b = np.ascontiguousarray(a, np.float32).view(np.uint32), np.ascontiguousarray(b, np.float32).view(np.uint32)
+    if not np.array_equal(a, b):
+        bad = np.argwhere(a != b)
+        raise AssertionError(f"{what}: {len(bad)} of {a.size} values differ, first at {tuple(int(x) for x in bad[0])}")
+
+
+def field(shape, seed=0):
+    return (np.random.default_rng(seed).standard_normal(shape) * 1e3).astype(np.float32)
+
+
+SHAPES = [(3, 3, 4), (4, 5, 8), (9, 11, 12), (20, 20, 20), (7, 40, 132), (33, 18, 260), (12, 70, 128), (40, 37, 516)]
+
+
+@pytest.mark.parametrize("arith", [0, 1, 2])
+def test_updates_bit_exact_vs_the_3d_oracle(ph, oracle, arith):
+    for shape in SHAPES:
+        u = field(shape, seed=sum(shape))
+        for steps in (1, 2, 5):
+            want, wd, _ = oracle.solve3d(u, steps, arith=arith, cx=0.1, cy=0.07, cz=0.05)
+            got, done, _ = ph.solve(u, steps, arith=arith, cx=0.1, cy=0.07, cz=0.05)
+            assert done == wd == steps and got.shape == shape
+            same_bits(got, want, f"3-D {shape} steps={steps} arith={arith}")
+            for ax in range(3):
+                for face in (0, -1):
+                    same_bits(np.take(got, face, axis=ax), np.take(u, face, axis=ax), "ring face")
+
+
+def test_inidat_handle_api_and_convergence(ph, oracle):
+    for shape in [(20, 20, 20), (40, 33, 64), (130, 70, 36)]:
+        with ph.HeatSolver(shape[0], shape[1], nz=shape[2]) as s:
+            s.init_inidat()
+            u = s.download()
+            assert u.shape == shape
+            same_bits(u, oracle.inidat3d(*shape), f"inidat3d {shape}")
+            same_bits(u, ph.inidat3d(*shape), f"host inidat3d {shape}")
+            assert s.run(7) == (7, False)
+            same_bits(s.download(), oracle.solve3d(u, 7, arith=0)[0], f"run {shape}")
+    u = ph.inidat3d(12, 12, 12)
+    want, wd, wc = oracle.solve3d(u, 100000, arith=2, conv_every=20, conv_phase=0, step_convention=1)
+    got, done, conv = ph.solve(u, 100000, arith=ph.MPI_F64MIX, conv_every=20, conv_phase=ph.PHASE_MPI, step_convention=ph.STEPS_MPI)
+    assert wc and (done, conv) == (wd, wc)
+    same_bits(got, want, "converged 3-D field")
+    with pytest.raises(ph.HeatError):
+        ph.HeatSolver(20, 20, nz=6)  # nz must be a multiple of 4
+    with pytest.raises(ph.HeatError):
+        ph.HeatSolver(20, 20, nz=8, temporal_block=2)
+
+
+def test_streaming_and_plane_tiles_do_not_change_bits(ph, oracle, monkeypatch):
+    u = field((300, 24, 36), seed=9)
+    want, _, _ = oracle.solve3d(u, 12, arith=1)
+    for band in (0, 8, 13, 64):
+        if band:
+            monkeypatch.setenv("HEAT_SOLVE_BAND_ROWS", str(band))
+        same_bits(ph.solve(u, 12, arith=1)[0], want, f"streamed band={band}")
+    monkeypatch.delenv("HEAT_SOLVE_BAND_ROWS")
+    monkeypatch.setenv("HEAT_SOLVE_STREAMED", "0")
+    same_bits(ph.solve(u, 12, arith=1)[0], want, "plain loop")
+
+
+def test_512_cubed_slab_matches_the_oracle(ph, oracle):
+    n, k = 512, 6
+    with ph.HeatSolver(n, n, nz=n) as s:
+        s.init_inidat()
+        s.run(k)
+        got = s.download()
+    ini = oracle.inidat3d(n, n, n)
+    for x0 in (0, 250, n - 20):
+        lo, hi = max(0, x0 - k), min(n, x0 + 20 + k)
+        want, _, _ = oracle.solve3d(ini[lo:hi], k, arith=0)
+        same_bits(got[x0:x0 + 20], want[x0 - lo:x0 - lo + 20], f"512^3 planes {x0}..")

@@ -183,3 +183,41 @@ def test_reference_ranks_convergence_and_baseline_config(oracle, golden):
     e = [x for x in golden["plain"] if x["nx"] == 1024 and x["steps"] == 1000][0]
     r = oracle.run_reference("mpi", 1024, 1024, 1000, ranks=4, text=True, capture=False)
     assert r["final_text_md5"] == e["final_text_md5"] == "e2c85256585896d5183a3006279cea23"
+
+
+def test_3d_oracle_against_a_numpy_restatement(oracle):
+    # the 3-D mode has no reference to be pinned to (the reference is 2-D); at least its two unfused arithmetics
+    # must agree bit for bit with an independent numpy statement of the same expression, and reduce to the 2-D
+    # update when nothing varies along z
+    rng = np.random.default_rng(3)
+    u = (rng.standard_normal((9, 11, 12)) * 1e3).astype(np.float32)
+    cx, cy, cz = np.float32(0.1), np.float32(0.07), np.float32(0.05)
+    c = u[1:-1, 1:-1, 1:-1]
+    xs = u[2:, 1:-1, 1:-1] + u[:-2, 1:-1, 1:-1]
+    ys = u[1:-1, 2:, 1:-1] + u[1:-1, :-2, 1:-1]
+    zs = u[1:-1, 1:-1, 2:] + u[1:-1, 1:-1, :-2]
+    two = np.float32(2.0)
+    want1 = u.copy()
+    want1[1:-1, 1:-1, 1:-1] = ((c + cx * (xs - two * c)) + cy * (ys - two * c)) + cz * (zs - two * c)
+    got1, done, _ = oracle.solve3d(u, 1, arith=oracle.F32_NOFMA, cx=cx, cy=cy, cz=cz)
+    assert done == 1 and np.array_equal(got1.view(np.uint32), want1.view(np.uint32))
+    cd = c.astype(np.float64)
+    r = cd + np.float64(cx) * (xs.astype(np.float64) - 2.0 * cd)
+    r = r + np.float64(cy) * (ys.astype(np.float64) - 2.0 * cd)
+    r = r + np.float64(cz) * (zs.astype(np.float64) - 2.0 * cd)
+    want2 = u.copy()
+    want2[1:-1, 1:-1, 1:-1] = r.astype(np.float32)
+    got2, _, _ = oracle.solve3d(u, 1, arith=oracle.MPI_F64MIX, cx=cx, cy=cy, cz=cz)
+    assert np.array_equal(got2.view(np.uint32), want2.view(np.uint32))
+    # the ring (all six faces) is never written
+    for g in (got1, got2):
+        for ax in range(3):
+            for face in (0, -1):
+                assert np.array_equal(np.take(g, face, axis=ax).view(np.uint32), np.take(u, face, axis=ax).view(np.uint32))
+    # constant along z with cz*0: every z-slice evolves like the 2-D field
+    v = (rng.standard_normal((10, 13)) * 1e2).astype(np.float32)
+    v3 = np.repeat(v[:, :, None], 8, axis=2)
+    a3, _, _ = oracle.solve3d(v3, 5, arith=oracle.F32_NOFMA, cz=0.0)
+    a2, _, _ = oracle.solve(v, 5, arith=oracle.F32_NOFMA)
+    assert np.allclose(a3[:, :, 3], a2, rtol=1e-6, atol=1e-4)  # (+ cz*0 adds a rounding-free zero: equal up to -0.0)
+    assert np.array_equal(oracle.inidat3d(5, 6, 8)[2, 3], (2 * 2 * 3 * 2 * np.arange(8) * (7 - np.arange(8))).astype(np.float32))
