@@ -525,7 +525,7 @@ def run_one(ctx, api, wl, arith, args):
         own_lups = (min(rows_own, nx - 2) if world > 1 else nx - 2) * min(cols_own, ny - 2) * T
         kernel_ms = ms / max(step_launches, 1)
         achieved = bytes_per_lup * own_lups / (kernel_ms * 1e-3) / 1e9
-        staged = ny >= 16384 and arith != api.MPI_F64MIX and args.cols == 1 and os.environ.get("HEAT_K1_VARIANT", "auto") in ("", "auto")
+        staged = ny >= 16384 and arith != api.MPI_F64MIX and world == 1 and os.environ.get("HEAT_K1_VARIANT", "auto") in ("", "auto")
         staged = staged or os.environ.get("HEAT_K1_VARIANT") == "bulk"
         kname = "heat_step_tb" if T > 1 else "heat_step_f64" if es == 8 else "heat_step_bulk" if staged else "heat_step_vec"
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,

@@ -544,8 +544,11 @@ static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, fl
     // column blocks are not.
     // (MPI_F64MIX: measured slower staged, 680 vs 732 GLUP/s at 16384^2 -- its warps are busy converting, and the
     // staged form has fewer loads in flight per warp -- so "auto" keeps that mode on K1)
+    // Flag-ordered strips: measured on 2 GPUs at 65536^2 K1 1711 vs K1b 1690 GLUP/s with three times the spread between
+    // repetitions, so "auto" stages only on a single strip.
     const bool bulk = h->p.nranks_y == 1 &&
-                      (h->k1_variant == 1 || (h->k1_variant == 2 && h->pitch >= BULK_MIN_PITCH && ARITH != HEAT_ARITH_F64MIX));
+                      (h->k1_variant == 1 || (h->k1_variant == 2 && h->pitch >= BULK_MIN_PITCH && ARITH != HEAT_ARITH_F64MIX &&
+                                              h->p.nranks == 1));
     if (bulk) {
         constexpr int ROWS = HEAT_BULK_ROWS;
         if (h->ghost <= ROWS && (rows + ROWS - 1) / ROWS <= 65535) {
