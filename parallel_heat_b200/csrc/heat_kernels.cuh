@@ -1344,6 +1344,10 @@ heat_step_3d(const float* __restrict__ in, float* __restrict__ out, int plane_lo
                 float wl = __shfl_up_sync(FULL, c[k].w, 1);
                 float er = __shfl_down_sync(FULL, c[k].x, 1);
                 if (y < ny - 1) {
+                    // the ring rows iy = 0 and ny-1 are written back unchanged by their neighbours' owner (like the
+                    // ring columns below), so that `out` needs no copy of the field beforehand
+                    if (y == 1 && live) st4(q + roff[0], c[0]);
+                    if (y == ny - 2 && live) st4(q + roff[k + 1], c[k + 1]);
                     if (e0) wl = ld1(pc + roff[k] - 1);
                     if (e31) er = ld1(pc + roff[k] + 4);
                     const float4 cc = c[k], up = c[k - 1], dn = c[k + 1], xm = n[k - 1], xp = s[k];
