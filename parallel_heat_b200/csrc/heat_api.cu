@@ -686,10 +686,10 @@ static cudaError_t launch_step_3d_t(heat_handle* h, const float* in, float* out)
     const int planes = h->upd_hi - h->upd_lo, ny = h->ny3, nz = h->nz;
     if (planes < 1 || ny < 3 || nz < 4) return cudaSuccess;
 #ifndef HEAT_3D_TY
-#define HEAT_3D_TY 4 // iy rows per thread
-#endif
+#define HEAT_3D_TY 2 // iy rows per thread.  Measured at 640^3 / 1024^3 (GLUP/s): TY 2 x 8 warps 631 / 627, 2 x 4 579 / 589,
+#endif               // 4 x 4 557 / 566 (123 registers), 8 x 4 345 / 349 (190 registers): occupancy beats fewer halo loads
 #ifndef HEAT_3D_WARPS
-#define HEAT_3D_WARPS 4
+#define HEAT_3D_WARPS 8
 #endif
     constexpr int TY = HEAT_3D_TY, WARPS = HEAT_3D_WARPS;
     // plane tiles: many more CTAs than fit at once (the tail of a 1.35-wave grid cost a quarter of the time), tiles
