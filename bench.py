@@ -418,13 +418,15 @@ def device_window(torch, ptr, pitch, r0, r1, c0, c1, device, es=4):
     return torch.as_tensor(a, device=f"cuda:{device}").cpu().numpy()
 
 
-def inidat_window(nx, ny, r0, r1, c0, c1):
-    """inidat (M:320, int32 wrap included) on a window of the global grid."""
+def inidat_window(nx, ny, r0, r1, c0, c1, dtype=None):
+    """inidat (M:320, int32 wrap included) on a window of the global grid; dtype float64 for double grids (the int
+    product converts exactly there, it is rounded only for float)."""
     import numpy as np
+    dtype = dtype or np.float32
     ix = np.arange(r0, r1, dtype=np.uint32)[:, None]
     iy = np.arange(c0, c1, dtype=np.uint32)[None, :]
     prod = ix * (np.uint32(nx) - ix - np.uint32(1)) * iy * (np.uint32(ny) - iy - np.uint32(1))
-    return prod.view(np.int32).astype(np.float32)
+    return prod.view(np.int32).astype(dtype)
 
 
 def parity_windows(ctx, wl, arith, view, updates, get):
@@ -449,9 +451,9 @@ def parity_windows(ctx, wl, arith, view, updates, get):
     for (r0, r1) in sorted(rows):
         for (c0, c1) in sorted(cols):
             R0, R1, C0, C1 = max(0, r0 - U), min(nx, r1 + U), max(0, c0 - U), min(ny, c1 + U)
-            ini = inidat_window(nx, ny, R0, R1, C0, C1)
+            ini = inidat_window(nx, ny, R0, R1, C0, C1, np.float64 if wl.get("f64") else np.float32)
             if wl.get("f64"):  # double grids: the oracle's double mode (parity unpinned, see oracle/heat_oracle.c)
-                want, _, _ = O.solve_f64(ini.astype(np.float64), U, fused=(arith == 0))
+                want, _, _ = O.solve_f64(ini, U, fused=(arith == 0))
             else:
                 want, _, _ = O.solve(ini, U, arith=arith)
             want = want[r0 - R0:r1 - R0, c0 - C0:c1 - C0]

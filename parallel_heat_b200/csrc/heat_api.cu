@@ -685,11 +685,19 @@ static cudaError_t launch_step_3d_t(heat_handle* h, const float* in, float* out)
 {
     const int planes = h->upd_hi - h->upd_lo, ny = h->ny3, nz = h->nz;
     if (planes < 1 || ny < 3 || nz < 4) return cudaSuccess;
-    constexpr int TY = 4, WARPS = 4;
-    // plane tiles: enough CTAs for a few waves, tiles no shorter than 8 planes (two planes of halo per tile)
+#ifndef HEAT_3D_TY
+#define HEAT_3D_TY 2 // iy rows per thread.  Measured at 640^3 / 1024^3 (GLUP/s): TY 2 x 8 warps 631 / 627, 2 x 4 579 / 589,
+#endif               // 4 x 4 557 / 566 (123 registers), 8 x 4 345 / 349 (190 registers): occupancy beats fewer halo loads
+#ifndef HEAT_3D_WARPS
+#define HEAT_3D_WARPS 8
+#endif
+    constexpr int TY = HEAT_3D_TY, WARPS = HEAT_3D_WARPS;
+    // plane tiles: many more CTAs than fit at once (the tail of a 1.35-wave grid cost a quarter of the time), tiles
+    // no shorter than 16 planes (two planes of halo per tile); HEAT_3D_PLANES overrides
     const long long ctas_xy = (long long)((nz / 4 + 31) / 32) * ((ny - 2 + TY * WARPS - 1) / (TY * WARPS));
     int ppt = planes;
-    while (ppt > 8 && ctas_xy * ((planes + ppt - 1) / ppt) < 4LL * h->sm_count) ppt = (ppt + 1) / 2;
+    while (ppt > 16 && ctas_xy * ((planes + ppt - 1) / ppt) < 40LL * h->sm_count) ppt = (ppt + 1) / 2;
+    if (env_int("HEAT_3D_PLANES", 0) > 0) ppt = env_int("HEAT_3D_PLANES", 0);
     if ((planes + ppt - 1) / ppt > 65535) ppt = (planes + 65534) / 65535;
     dim3 grid((unsigned)((nz / 4 + 31) / 32), (unsigned)((ny - 2 + TY * WARPS - 1) / (TY * WARPS)), (unsigned)((planes + ppt - 1) / ppt));
     heat_step_3d<ARITH, RESID, TY, WARPS><<<grid, 32 * WARPS, 0, h->stream>>>(in, out, h->upd_lo, h->upd_hi, ny, nz, h->pitch, ppt, h->p.cx,

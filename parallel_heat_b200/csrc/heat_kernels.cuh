@@ -1260,9 +1260,9 @@ heat_absdiff_max_f64(const double* __restrict__ a, const double* __restrict__ b,
 // neighbour sums, the rest in double).  All six faces are the ring.  A "row" of the handle is one ix-plane
 // (ny*nz floats), so upload, download, the streamed one-shot and the residual pass are the 2-D ones.
 // Register-blocked column streaming, one dimension up: lanes run along iz (one float4 each), a thread owns TY
-// consecutive iy rows of its four columns and streams along ix with the previous, current and next plane of
+// (2) consecutive iy rows of its four columns and streams along ix with the previous, current and next plane of
 // those rows in registers.  Y neighbours inside the thread's rows are its own registers, the two rows beyond
-// come with the plane (TY+2 loads for TY outputs, the extra ones L1/L2 hits of the neighbouring warps), Z
+// come with the plane (TY+2 loads for TY outputs: 4 for 2, the extra ones L1/L2 hits of the neighbouring warps), Z
 // neighbours are shuffles (across the warp edge: one 4-byte load).  No shared memory.
 template <int ARITH>
 __device__ __forceinline__ float upd3(float c, float xs, float ys, float zs, float cx, float cy, float cz)
@@ -1344,6 +1344,10 @@ heat_step_3d(const float* __restrict__ in, float* __restrict__ out, int plane_lo
                 float wl = __shfl_up_sync(FULL, c[k].w, 1);
                 float er = __shfl_down_sync(FULL, c[k].x, 1);
                 if (y < ny - 1) {
+                    // the ring rows iy = 0 and ny-1 are written back unchanged by their neighbours' owner (like the
+                    // ring columns below), so that `out` needs no copy of the field beforehand
+                    if (y == 1 && live) st4(q + roff[0], c[0]);
+                    if (y == ny - 2 && live) st4(q + roff[k + 1], c[k + 1]);
                     if (e0) wl = ld1(pc + roff[k] - 1);
                     if (e31) er = ld1(pc + roff[k] + 4);
                     const float4 cc = c[k], up = c[k - 1], dn = c[k + 1], xm = n[k - 1], xp = s[k];
