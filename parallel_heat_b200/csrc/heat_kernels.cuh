@@ -249,9 +249,35 @@ __device__ __forceinline__ void st4(float* p, float4 v)
     if (inside(p, 4, 1, 3)) *reinterpret_cast<float4*>(p) = v;
 }
 #else
-__device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+// Cache policy of the field's loads and stores (build-time; 0 = plain).  Every byte is read once and written once
+// per pass, so streaming hints (evict-first) are the candidates; measured in round 2, see DESIGN.md section 3.
+#ifndef HEAT_LD_POLICY
+#define HEAT_LD_POLICY 0 // 1 = ld.global.cs (evict first), 2 = ld.global.nc (read-only path)
+#endif
+#ifndef HEAT_ST_POLICY
+#define HEAT_ST_POLICY 0 // 1 = st.global.cs (evict first), 2 = st.global.wt (write through)
+#endif
+__device__ __forceinline__ float4 ld4(const float* p)
+{
+#if HEAT_LD_POLICY == 1
+    return __ldcs(reinterpret_cast<const float4*>(p));
+#elif HEAT_LD_POLICY == 2
+    return __ldg(reinterpret_cast<const float4*>(p));
+#else
+    return *reinterpret_cast<const float4*>(p);
+#endif
+}
 __device__ __forceinline__ float ld1(const float* p) { return *p; }
-__device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+__device__ __forceinline__ void st4(float* p, float4 v)
+{
+#if HEAT_ST_POLICY == 1
+    __stcs(reinterpret_cast<float4*>(p), v);
+#elif HEAT_ST_POLICY == 2
+    __stwt(reinterpret_cast<float4*>(p), v);
+#else
+    *reinterpret_cast<float4*>(p) = v;
+#endif
+}
 #endif
 
 // ------------------------------------------------------------------ K0 inidat
