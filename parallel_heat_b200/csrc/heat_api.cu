@@ -544,8 +544,8 @@ static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, fl
     // column blocks are not.
     // (MPI_F64MIX: measured slower staged, 680 vs 732 GLUP/s at 16384^2 -- its warps are busy converting, and the
     // staged form has fewer loads in flight per warp -- so "auto" keeps that mode on K1)
-    // Flag-ordered strips: measured on 2 GPUs at 65536^2 K1 1711 vs K1b 1690 GLUP/s with three times the spread between
-    // repetitions, so "auto" stages only on a single strip.
+    // Flag-ordered strips: measured on 2 GPUs at 65536^2, three alternating runs of 21 repetitions each: K1 1704 GLUP/s
+    // (repetitions 50.2-51.7 ms), K1b 1635 (49.9-55.4 ms), so "auto" stages only on a single strip.
     const bool bulk = h->p.nranks_y == 1 &&
                       (h->k1_variant == 1 || (h->k1_variant == 2 && h->pitch >= BULK_MIN_PITCH && ARITH != HEAT_ARITH_F64MIX &&
                                               h->p.nranks == 1));

@@ -723,6 +723,9 @@ heat_step_bulk(const float* __restrict__ in, float* __restrict__ out, int row_lo
     if (SYNC) strip_wait(sy, edge_n, edge_s); // the ghost rows this tile reads are the neighbour's previous pass
     __syncthreads();
     if (tid == 0) {
+        // the neighbour's ghost-row stores were observed through the generic proxy (the flag's ld.acquire); the row
+        // copies below read through the async proxy, which needs its own fence to be ordered behind that
+        if (SYNC && (edge_n || edge_s)) asm volatile("fence.proxy.async;" ::: "memory");
         ptx::mbarrier_arrive_expect_tx(ptx::sem_release, ptx::scope_cta, ptx::space_shared, &bar, row_bytes * (unsigned)(nrows + 2));
         for (int i = 0; i < nrows + 2; i++)
             ptx::cp_async_bulk(ptx::space_cluster, ptx::space_global, tile + i * SW + (c_lo - (col0 - HALO)),
