@@ -1335,8 +1335,11 @@ __global__ void heat_inidat3d_kernel(float* __restrict__ a, float* __restrict__ 
 
 //   grid.x = ceil(nz/4 / 32), grid.y = ceil((ny-2) / (TY*WARPS)), grid.z = plane tiles; block = 32*WARPS
 //   planes [plane_lo, plane_hi) are updated (planes plane_lo-1 and plane_hi must exist)
+#ifndef HEAT_3D_MINBLOCKS
+#define HEAT_3D_MINBLOCKS 1
+#endif
 template <int ARITH, bool RESID, int TY, int WARPS>
-__global__ void __launch_bounds__(32 * WARPS)
+__global__ void __launch_bounds__(32 * WARPS, HEAT_3D_MINBLOCKS)
 heat_step_3d(const float* __restrict__ in, float* __restrict__ out, int plane_lo, int plane_hi, int ny, int nz, int64_t pitch,
              int planes_per_tile, float cx, float cy, float cz, unsigned* __restrict__ resid)
 {
@@ -1352,9 +1355,9 @@ heat_step_3d(const float* __restrict__ in, float* __restrict__ out, int plane_lo
         const bool kx = (col == 0), kw = (col + 3 == nz - 1); // ring columns iz = 0 and nz-1: copied through
         const bool e0 = lane == 0 && col > 0, e31 = lane == 31 && col + 4 < nz;
         // rows y0-1 .. y0+TY of a plane; rows past ny-1 are clamped (loaded, never used for a store)
-        int64_t roff[TY + 2];
+        int roff[TY + 2]; // offsets inside a plane: ny*nz fits an int (checked by heat_create)
 #pragma unroll
-        for (int k = 0; k < TY + 2; k++) roff[k] = (int64_t)min(y0 - 1 + k, ny - 1) * nz + col;
+        for (int k = 0; k < TY + 2; k++) roff[k] = min(y0 - 1 + k, ny - 1) * nz + col;
         float4 n[TY], c[TY + 2], s[TY + 2];
         const float* pn = in + (int64_t)(x0 - 1) * pitch;
 #pragma unroll
