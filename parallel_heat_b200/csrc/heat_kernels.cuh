@@ -1339,8 +1339,9 @@ __global__ void heat_inidat3d_kernel(float* __restrict__ a, float* __restrict__ 
 // Strips of planes across GPUs work like the 2-D row strips (K3): the first / last owned plane is also stored into
 // the neighbour's ghost plane, the tiles that touch a neighbour wait for its flag and the last of them raises it.
 #ifndef HEAT_3D_MINBLOCKS
-#define HEAT_3D_MINBLOCKS 1
-#endif
+#define HEAT_3D_MINBLOCKS 4 // resident CTAs per SM asked of the compiler: 4 = 64 registers, no spills.  Measured at 640^3 /
+#endif                      // 1024^3: unconstrained (78 registers, 3 CTAs) 649 / 652 GLUP/s, 4: 716 / 709, 5 (48 registers, spills) 450 / 449
+
 template <int ARITH, bool RESID, int TY, int WARPS, bool SYNC>
 __global__ void __launch_bounds__(32 * WARPS, HEAT_3D_MINBLOCKS)
 heat_step_3d(const float* __restrict__ in, float* __restrict__ out, int plane_lo, int plane_hi, int ny, int nz, int64_t pitch,
