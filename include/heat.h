@@ -49,7 +49,7 @@ extern "C" {
 /* 3-D grids (the reference is 2-D only): nz > 1 makes the grid nx*ny*nz, dense, iz fastest,
  * and the update the 7-point one, new = u + cx*((X+ + X-) - 2u) + cy*((Y+ + Y-) - 2u) + cz*((Z+ + Z-) - 2u),
  * evaluated left to right in the arithmetic `arith` names (F32_FMA: three fused multiply-adds); all six faces
- * are the ring.  nz must be a multiple of 4; one GPU, float, single updates (nranks 1, nranks_y 1,
+ * are the ring.  nz must be a multiple of 4; float, single updates, one strip or strips of ix-planes (nranks_y 1,
  * temporal_block 1).  heat_solve, heat_upload, heat_download, heat_init_inidat, heat_run and the convergence
  * check work as in 2-D on the nx*ny*nz array. */
 

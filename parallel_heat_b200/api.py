@@ -284,7 +284,7 @@ class HeatSolver:
         _check(load().heat_upload_local(self._h, p))
 
     def download_local(self, out):
-        """out: (rows this strip owns, ny) float32, C-contiguous."""
+        """out: (rows this strip owns, ny) float32, C-contiguous (3-D grids: (planes owned, ny*nz))."""
         assert out.dtype == np.float32 and out.flags.c_contiguous
         _check(load().heat_download_local(self._h, out.ctypes.data_as(_fp)))
         return out

@@ -332,8 +332,8 @@ static int validate(const heat_params* p)
     if (p->nz > 1) {
         if (p->nz % 4 || p->nz < 4) return fail(HEAT_E_INVALID, "params: nz=%d (3-D grids need nz a multiple of 4)", p->nz);
         if ((long long)p->ny * p->nz > 0x7fffffffLL) return fail(HEAT_E_INVALID, "params: ny*nz=%lld does not fit an int", (long long)p->ny * p->nz);
-        if (p->nranks != 1 || p->nranks_y != 1 || p->temporal_block != 1 || p->grid_type != HEAT_GRID_F32)
-            return fail(HEAT_E_INVALID, "params: 3-D grids run single float updates on one GPU (nranks 1, nranks_y 1, temporal_block 1)");
+        if (p->nranks_y != 1 || p->temporal_block != 1 || p->grid_type != HEAT_GRID_F32)
+            return fail(HEAT_E_INVALID, "params: 3-D grids run single float updates on strips of planes (nranks_y 1, temporal_block 1)");
     }
     if (p->conv_phase != HEAT_PHASE_MPI && p->conv_phase != HEAT_PHASE_CUDA)
         return fail(HEAT_E_INVALID, "params: conv_phase=%d", p->conv_phase);
@@ -681,7 +681,7 @@ static cudaError_t launch_step_f64_t(heat_handle* h, const float* in, float* out
 
 // 3-D 7-point update: planes [upd_lo, upd_hi) of the handle's rows
 template <int ARITH, bool RESID>
-static cudaError_t launch_step_3d_t(heat_handle* h, const float* in, float* out)
+static cudaError_t launch_step_3d_t(heat_handle* h, const float* in, float* out, float* peer_n, float* peer_s)
 {
     const int planes = h->upd_hi - h->upd_lo, ny = h->ny3, nz = h->nz;
     if (planes < 1 || ny < 3 || nz < 4) return cudaSuccess;
@@ -700,28 +700,34 @@ static cudaError_t launch_step_3d_t(heat_handle* h, const float* in, float* out)
     if (env_int("HEAT_3D_PLANES", 0) > 0) ppt = env_int("HEAT_3D_PLANES", 0);
     if ((planes + ppt - 1) / ppt > 65535) ppt = (planes + 65534) / 65535;
     dim3 grid((unsigned)((nz / 4 + 31) / 32), (unsigned)((ny - 2 + TY * WARPS - 1) / (TY * WARPS)), (unsigned)((planes + ppt - 1) / ppt));
-    heat_step_3d<ARITH, RESID, TY, WARPS><<<grid, 32 * WARPS, 0, h->stream>>>(in, out, h->upd_lo, h->upd_hi, ny, nz, h->pitch, ppt, h->p.cx,
-                                                                            h->p.cy, h->p.cz, h->d_resid);
+    // every CTA of the first / last plane tile touches the neighbour on that side (same predicate as in the kernel)
+    h->sync_args.count[0] = h->sync_args.count[1] = grid.x * grid.y;
+    if (h->sync_args.counters)
+        heat_step_3d<ARITH, RESID, TY, WARPS, true><<<grid, 32 * WARPS, 0, h->stream>>>(
+            in, out, h->upd_lo, h->upd_hi, ny, nz, h->pitch, ppt, h->p.cx, h->p.cy, h->p.cz, h->d_resid, peer_n, peer_s, h->sync_args);
+    else
+        heat_step_3d<ARITH, RESID, TY, WARPS, false><<<grid, 32 * WARPS, 0, h->stream>>>(
+            in, out, h->upd_lo, h->upd_hi, ny, nz, h->pitch, ppt, h->p.cx, h->p.cy, h->p.cz, h->d_resid, peer_n, peer_s, h->sync_args);
     h->launches++;
     return cudaGetLastError();
 }
 
-static cudaError_t launch_step_3d(heat_handle* h, bool resid, const float* in, float* out)
+static cudaError_t launch_step_3d(heat_handle* h, bool resid, const float* in, float* out, float* pn, float* ps)
 {
     switch (h->p.arith * 2 + (resid ? 1 : 0)) {
-    case 0: return launch_step_3d_t<HEAT_ARITH_F32_FMA, false>(h, in, out);
-    case 1: return launch_step_3d_t<HEAT_ARITH_F32_FMA, true>(h, in, out);
-    case 2: return launch_step_3d_t<HEAT_ARITH_F32_NOFMA, false>(h, in, out);
-    case 3: return launch_step_3d_t<HEAT_ARITH_F32_NOFMA, true>(h, in, out);
-    case 4: return launch_step_3d_t<HEAT_ARITH_F64MIX, false>(h, in, out);
-    default: return launch_step_3d_t<HEAT_ARITH_F64MIX, true>(h, in, out);
+    case 0: return launch_step_3d_t<HEAT_ARITH_F32_FMA, false>(h, in, out, pn, ps);
+    case 1: return launch_step_3d_t<HEAT_ARITH_F32_FMA, true>(h, in, out, pn, ps);
+    case 2: return launch_step_3d_t<HEAT_ARITH_F32_NOFMA, false>(h, in, out, pn, ps);
+    case 3: return launch_step_3d_t<HEAT_ARITH_F32_NOFMA, true>(h, in, out, pn, ps);
+    case 4: return launch_step_3d_t<HEAT_ARITH_F64MIX, false>(h, in, out, pn, ps);
+    default: return launch_step_3d_t<HEAT_ARITH_F64MIX, true>(h, in, out, pn, ps);
     }
 }
 
 static cudaError_t launch_step(heat_handle* h, bool resid, const float* in, float* out, float* peer_n, float* peer_s,
                                int reverse)
 {
-    if (h->nz > 1) return launch_step_3d(h, resid, in, out);
+    if (h->nz > 1) return launch_step_3d(h, resid, in, out, peer_n, peer_s);
     if (h->es == 2) {
         const bool fma = h->p.arith == HEAT_F32_FMA;
         return fma ? (resid ? launch_step_f64_t<true, true>(h, in, out, peer_n, peer_s, reverse)
@@ -1334,7 +1340,7 @@ extern "C" int heat_init_inidat(heat_handle* h)
         if (rc) return rc;
     }
     if (h->nz > 1)
-        heat_inidat3d_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(h->buf[0], h->buf[1], h->p.nx, h->ny3, h->nz, h->nloc, h->pitch);
+        heat_inidat3d_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(h->buf[0], h->buf[1], h->p.nx, h->ny3, h->nz, h->lo, h->nloc, h->pitch);
     else if (h->es == 2)
         heat_inidat_f64_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>((double*)h->buf[0], (double*)h->buf[1], h->p.nx, h->p.ny, h->lo,
                                                                        h->nloc, h->pitch / 2, h->lo_c, h->nyloc);

@@ -1314,12 +1314,13 @@ __device__ __forceinline__ float upd3(float c, float xs, float ys, float zs, flo
     }
 }
 
-__global__ void heat_inidat3d_kernel(float* __restrict__ a, float* __restrict__ b, int nx, int ny, int nz, int nplanes, int64_t pitch)
+__global__ void heat_inidat3d_kernel(float* __restrict__ a, float* __restrict__ b, int nx, int ny, int nz, int plane_lo, int nplanes,
+                                     int64_t pitch)
 {
     const int64_t total = (int64_t)nplanes * pitch, plane = (int64_t)ny * nz;
     for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
-        const int ix = (int)(k / pitch);
-        const int64_t in_plane = k - (int64_t)ix * pitch;
+        const int lx = (int)(k / pitch), ix = plane_lo + lx; // local array = global planes [plane_lo, plane_lo + nplanes)
+        const int64_t in_plane = k - (int64_t)lx * pitch;
         float v = 0.0f;
         if (in_plane < plane) {
             const int iy = (int)(in_plane / nz), iz = (int)(in_plane - (int64_t)iy * nz);
@@ -1335,19 +1336,26 @@ __global__ void heat_inidat3d_kernel(float* __restrict__ a, float* __restrict__ 
 
 //   grid.x = ceil(nz/4 / 32), grid.y = ceil((ny-2) / (TY*WARPS)), grid.z = plane tiles; block = 32*WARPS
 //   planes [plane_lo, plane_hi) are updated (planes plane_lo-1 and plane_hi must exist)
+// Strips of planes across GPUs work like the 2-D row strips (K3): the first / last owned plane is also stored into
+// the neighbour's ghost plane, the tiles that touch a neighbour wait for its flag and the last of them raises it.
 #ifndef HEAT_3D_MINBLOCKS
-#define HEAT_3D_MINBLOCKS 1
-#endif
-template <int ARITH, bool RESID, int TY, int WARPS>
+#define HEAT_3D_MINBLOCKS 4 // resident CTAs per SM asked of the compiler: 4 = 64 registers, no spills.  Measured at 640^3 /
+#endif                      // 1024^3: unconstrained (78 registers, 3 CTAs) 649 / 652 GLUP/s, 4: 716 / 709, 5 (48 registers, spills) 450 / 449
+
+template <int ARITH, bool RESID, int TY, int WARPS, bool SYNC>
 __global__ void __launch_bounds__(32 * WARPS, HEAT_3D_MINBLOCKS)
 heat_step_3d(const float* __restrict__ in, float* __restrict__ out, int plane_lo, int plane_hi, int ny, int nz, int64_t pitch,
-             int planes_per_tile, float cx, float cy, float cz, unsigned* __restrict__ resid)
+             int planes_per_tile, float cx, float cy, float cz, unsigned* __restrict__ resid, float* peer_n, float* peer_s,
+             strip_sync sy)
 {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int col = ((int)blockIdx.x * 32 + lane) * 4;                    // my first iz
     const int y0 = 1 + ((int)blockIdx.y * WARPS + warp) * TY;         // my first iy (interior rows start at 1)
-    const int x0 = plane_lo + (int)blockIdx.z * planes_per_tile, x1 = min(x0 + planes_per_tile, plane_hi);
+    const int tile = tile_of_block<SYNC>((int)blockIdx.z, (int)gridDim.z, 0); // with flags: the two edge tiles first
+    const int x0 = plane_lo + tile * planes_per_tile, x1 = min(x0 + planes_per_tile, plane_hi);
+    const bool edge_n = x0 == plane_lo, edge_s = x1 == plane_hi; // one ghost plane per neighbour (single updates)
+    if (SYNC) strip_wait(sy, edge_n, edge_s);
     float m = 0.0f;
     const bool live = col < nz;
     if (y0 < ny - 1 && col - lane * 4 < nz) { // else this warp has no row / no column to update (warp-uniform)
@@ -1390,7 +1398,11 @@ heat_step_3d(const float* __restrict__ in, float* __restrict__ out, int plane_lo
                     o.w = upd3<ARITH>(cc.w, __fadd_rn(xp.w, xm.w), __fadd_rn(dn.w, up.w), __fadd_rn(er, cc.z), cx, cy, cz);
                     if (kx) o.x = cc.x;
                     if (kw) o.w = cc.w;
-                    if (live) st4(q + roff[k], o);
+                    if (live) {
+                        st4(q + roff[k], o);
+                        if (peer_n && x == plane_lo) st4(peer_n + roff[k], o);
+                        if (peer_s && x == plane_hi - 1) st4(peer_s + roff[k], o);
+                    }
                     if (RESID) {
                         m = fmaxf(m, fabsf(__fsub_rn(cc.x, o.x)));
                         m = fmaxf(m, fabsf(__fsub_rn(cc.y, o.y)));
@@ -1406,6 +1418,7 @@ heat_step_3d(const float* __restrict__ in, float* __restrict__ out, int plane_lo
         }
     }
     if (RESID) block_max_to_global(live ? m : 0.0f, resid);
+    if (SYNC) strip_signal(sy, edge_n, edge_s);
 }
 
 // ------------------------------------------------------------------ residual of two buffers

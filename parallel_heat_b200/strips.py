@@ -103,6 +103,10 @@ class StripSolver:
             raise ValueError("halo must be 'p2p' or 'sendrecv'")
         self.halo = halo if self.world > 1 else "none"
         self.nx, self.ny = nx, ny
+        self.nz = int(params.get("nz", 1) or 1)
+        self.row_len = ny * self.nz if self.nz > 1 else ny  # a 3-D grid is cut into strips of ix-planes of ny*nz floats
+        if self.nz > 1 and (cols > 1 or halo != "p2p"):
+            raise ValueError("3-D grids: strips of planes with halo='p2p' only")
         if device is None:
             device = 0
         self.device = device
@@ -221,7 +225,7 @@ class StripSolver:
             return self.solver.download(np.zeros((self.nx, self.ny), np.float32))
         if self.cols == 1:
             # a row strip hands over its own rows only: no rank but `dst` ever holds the whole field
-            part = self.solver.download_local(np.empty((self.rows, self.ny), np.float32))
+            part = self.solver.download_local(np.empty((self.rows, self.row_len), np.float32))
         else:
             mine = np.zeros((self.nx, self.ny), np.float32)
             self.solver.download(mine)
@@ -231,7 +235,8 @@ class StripSolver:
         self.dist.gather_object(part, parts, dst=dst, group=self.group)
         if self.rank != dst:
             return None
-        return np.concatenate([np.concatenate(parts[bx * self.cols:(bx + 1) * self.cols], axis=1) for bx in range(self.gx)], axis=0)
+        full = np.concatenate([np.concatenate(parts[bx * self.cols:(bx + 1) * self.cols], axis=1) for bx in range(self.gx)], axis=0)
+        return full.reshape(self.nx, self.ny, self.nz) if self.nz > 1 else full
 
     def close(self):
         self.solver.close()

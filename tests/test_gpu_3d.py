@@ -82,3 +82,37 @@ def test_512_cubed_slab_matches_the_oracle(ph, oracle):
         lo, hi = max(0, x0 - k), min(n, x0 + 20 + k)
         want, _, _ = oracle.solve3d(ini[lo:hi], k, arith=0)
         same_bits(got[x0:x0 + 20], want[x0 - lo:x0 - lo + 20], f"512^3 planes {x0}..")
+
+
+def test_strips_of_planes_on_one_gpu(ph, oracle):
+    # the 3-D grid cut into strips of ix-planes (ghost planes stored by the update kernel, events between strips)
+    u = field((70, 20, 36), seed=4)
+    for g, arith in [(2, 0), (3, 1), (5, 2)]:
+        want, _, _ = oracle.solve3d(u, 9, arith=arith)
+        ss = [ph.HeatSolver(70, 20, nz=36, rank=r, nranks=g, arith=arith) for r in range(g)]
+        try:
+            for r, s in enumerate(ss):
+                s.connect_local(ss[r - 1] if r else None, ss[r + 1] if r < g - 1 else None)
+            for s in ss:
+                s.upload(u)
+            assert ph.group_run(ss, 9)[0] == 9
+            out = np.zeros_like(u)
+            for s in ss:
+                s.download(out)
+        finally:
+            for s in ss:
+                s.close()
+        same_bits(out, want, f"{g} strips of planes, arith={arith}")
+    # device-side inidat of a strip uses the global plane index
+    ss = [ph.HeatSolver(40, 12, nz=16, rank=r, nranks=2) for r in range(2)]
+    try:
+        ss[0].connect_local(None, ss[1]); ss[1].connect_local(ss[0], None)
+        out = np.zeros((40, 12, 16), np.float32)
+        for s in ss:
+            s.init_inidat()
+        for s in ss:
+            s.download(out)
+    finally:
+        for s in ss:
+            s.close()
+    same_bits(out, oracle.inidat3d(40, 12, 16), "inidat3d in strips")

@@ -41,7 +41,9 @@ def _worker(rank, world, port, shape, steps, halo, params, out_path, cols=1):
     try:
         import parallel_heat_b200 as ph
         from parallel_heat_b200.strips import StripSolver
-        u = ph.inidat(*shape) if params.pop("inidat", True) else None
+        u = (ph.inidat3d(*shape) if len(shape) == 3 else ph.inidat(*shape)) if params.pop("inidat", True) else None
+        if len(shape) == 3:
+            params = dict(params, nz=shape[2])
         s = StripSolver(shape[0], shape[1], device=rank, halo=halo, cols=cols, **params)
         s.upload(u)
         done, conv = s.run(steps)
@@ -155,5 +157,20 @@ def test_long_runs_across_processes(tmp_path, oracle, ph, cols, shape, steps, pa
     mp.spawn(_worker, args=(world, _free_port(), shape, steps, "p2p", dict(params), str(out), cols), nprocs=world, join=True)
     r = np.load(out)
     want, wdone, _ = oracle.solve(oracle.inidat(*shape), steps, arith=params.get("arith", 0))
+    assert int(r["done"]) == wdone
+    assert np.array_equal(r["full"].view(np.uint32), want.view(np.uint32))
+
+
+@needs2
+@pytest.mark.timeout(600)
+def test_3d_strips_of_planes_across_processes(tmp_path, oracle, ph):
+    # 3-D grid, one process per GPU: ghost planes by peer stores, device-side step flags
+    import torch.multiprocessing as mp
+    world = min(ngpus(), 4)
+    shape, steps = (96, 40, 132), 60
+    out = tmp_path / "out.npz"
+    mp.spawn(_worker, args=(world, _free_port(), shape, steps, "p2p", dict(arith=1), str(out)), nprocs=world, join=True)
+    r = np.load(out)
+    want, wdone, _ = oracle.solve3d(oracle.inidat3d(*shape), steps, arith=1)
     assert int(r["done"]) == wdone
     assert np.array_equal(r["full"].view(np.uint32), want.view(np.uint32))
