@@ -754,7 +754,11 @@ def run_ours(args, wl, rank, world, local_rank):
         e2e = None
         if not args.no_e2e:
             if world == 1:
-                e2e = e2e_single(ctx, api, wl, arith, max(args.steps // wl["temporal_block"], 1) * wl["temporal_block"])
+                try:
+                    e2e = e2e_single(ctx, api, wl, arith, max(args.steps // wl["temporal_block"], 1) * wl["temporal_block"])
+                except (MemoryError, RuntimeError) as e:  # e.g. the host cannot pin a second copy of the field
+                    e2e = {"value": None, "unit": "GLUP/s", "h2d_bytes_per_step": None, "d2h_bytes_per_step": None,
+                           "error": repr(e)[:300]}
             elif args.cols == 1:
                 e2e = e2e_strips(ctx, api, wl, arith, args)
 
@@ -767,7 +771,11 @@ def run_ours(args, wl, rank, world, local_rank):
                 w = workload(name, 1)
                 if tb:
                     w["temporal_block"] = tb
-                r = run_one(ctx, api, w, arith_, args)
+                try:  # a side leg that cannot run (memory, a missing binary) must not take the headline down with it
+                    r = run_one(ctx, api, w, arith_, args)
+                except Exception as e:
+                    also[key] = {"value": None, "error": repr(e)[:300], "workload": w["text"]}
+                    return
                 r["workload"] = w["text"] + (f", {tb} updates per HBM pass" if tb else "")
                 r["arith"] = api.ARITH_NAMES[arith_]
                 r["note"] = note
@@ -793,7 +801,10 @@ def run_ours(args, wl, rank, world, local_rank):
                     leg("mpi_f64mix_c2_8192", "c2", api.MPI_F64MIX, "8192x8192 in the MPI program's arithmetic")
             leg("f64_grid_16384", "g16k_f64", arith, "SURVEY 8(f) rank 4: the same update on a DOUBLE-precision grid (16 B per point-update, "
                 "so the HBM roofline is half as many LUP/s); parity unpinned -- the reference has no double build")
-            also["grid3d_640"] = leg_3d(ctx, api, 640, arith, args, peak)
+            try:
+                also["grid3d_640"] = leg_3d(ctx, api, 640, arith, args, peak)
+            except Exception as e:
+                also["grid3d_640"] = {"value": None, "error": repr(e)[:300]}
             also["reference_cuda"] = reference_cuda_leg(peak)
 
         if world > 1 and not args.no_also and args.cols == 1 and wl["name"] != "weak32k":

@@ -31,3 +31,19 @@ def test_other_ranks_of_the_reference_arm_exit_quietly():
     pr = subprocess.run([sys.executable, str(ROOT / "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "5"],
                         capture_output=True, text=True, timeout=120, cwd=ROOT, env=env)
     assert pr.returncode == 0 and pr.stdout.strip() == ""
+
+
+def test_bench_inidat_window_is_the_oracles_inidat(oracle):
+    # bench.py checks windows of the timed field against the oracle started from inidat restricted to the window
+    import importlib.util
+    import numpy as np
+    spec = importlib.util.spec_from_file_location("bench_mod", ROOT / "bench.py")
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    full = oracle.inidat(700, 900)  # wraps int32 beyond 432
+    w = bench.inidat_window(700, 900, 430, 470, 500, 640)
+    assert w.dtype == np.float32 and np.array_equal(w.view(np.uint32), full[430:470, 500:640].view(np.uint32))
+    w64 = bench.inidat_window(700, 900, 430, 470, 500, 640, np.float64)
+    assert np.array_equal(w64, oracle.inidat_f64(700, 900)[430:470, 500:640])
+    assert bench.reference_grid(bench.workload("strong", 1))[:2] == (16384, 16384)
+    assert bench.reference_grid(bench.workload("c2", 1))[2] is None
