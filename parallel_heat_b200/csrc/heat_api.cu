@@ -533,7 +533,10 @@ static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, fl
 #ifndef HEAT_K1_THREADS
 #define HEAT_K1_THREADS 128
 #endif
-    constexpr int THREADS = HEAT_K1_THREADS, UNROLL = 4;
+#ifndef HEAT_F64MIX_UNROLL
+#define HEAT_F64MIX_UNROLL 4
+#endif
+    constexpr int THREADS = HEAT_K1_THREADS, UNROLL = ARITH == HEAT_ARITH_F64MIX ? HEAT_F64MIX_UNROLL : 4;
     int rpt = pick_rows_per_tile(h, THREADS);
     if (rpt < h->ghost) rpt = h->ghost;
     if ((rows + rpt - 1) / rpt > 65535) rpt = (rows + 65534) / 65535; // grid.y limit: taller tiles

@@ -504,10 +504,13 @@ __device__ __forceinline__ bool cols_first(int& bx, int& by, int gx, int gy, int
 // Rows [row_lo, row_hi) are updated (rows row_lo-1 and row_hi must exist: ring or ghost).
 //   grid.x = ceil(pitch/4 / THREADS), grid.y = number of row tiles, block = THREADS
 //   reverse != 0 walks the tiles bottom-up (alternate sweeps re-use what is left in L2).
+#ifndef HEAT_F64MIX_THREADS_PER_SM
+#define HEAT_F64MIX_THREADS_PER_SM 1024 // resident threads per SM asked of the compiler for MPI_F64MIX (64 registers)
+#endif
 template <int ARITH, bool RESID, int THREADS, int UNROLL, bool SYNC, bool COLS = false>
 // the plain single-strip update is held to 48 registers (40 warps per SM), the variants with the
 // residual or the strip flags to 56 (36 warps), the double-precision mode to 64
-__global__ void __launch_bounds__(THREADS, (ARITH == HEAT_ARITH_F64MIX ? 1024 : (SYNC || RESID || COLS) ? 1152 : 1280) / THREADS)
+__global__ void __launch_bounds__(THREADS, (ARITH == HEAT_ARITH_F64MIX ? HEAT_F64MIX_THREADS_PER_SM : (SYNC || RESID || COLS) ? 1152 : 1280) / THREADS)
 heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo, int row_hi, int ny, int64_t pitch,
               int rows_per_tile, float cx, float cy, unsigned* __restrict__ resid, float* peer_n, float* peer_s,
               int ghost, int reverse, strip_sync sy, col_peers cp = col_peers{})
