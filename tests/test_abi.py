@@ -137,3 +137,12 @@ def test_product_never_imports_the_oracle():
             + list((ROOT / "src").rglob("*.c")) + [ROOT / "include" / "heat.h"]:
         text = f.read_text()
         assert "pyoracle" not in text and "heat_oracle" not in text and "oracle/" not in text.replace("oracle/_ref", ""), f
+
+
+def test_host_inidat_twins_match_the_oracle(ph, oracle):
+    # heat_inidat_f64 / heat_inidat3d: the int product of M:320 (wrap included), stored as double / with a third factor pair
+    assert np.array_equal(ph.inidat_f64(500, 433), oracle.inidat_f64(500, 433))
+    assert np.array_equal(ph.inidat_f64(500, 433).astype(np.float32).view(np.uint32), ph.inidat(500, 433).view(np.uint32))
+    a, b = ph.inidat3d(33, 40, 52), oracle.inidat3d(33, 40, 52)
+    assert a.shape == (33, 40, 52) and np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    assert (a[0] == 0).all() and (a[:, 0] == 0).all() and (a[:, :, -1] == 0).all()  # the ring starts at zero
