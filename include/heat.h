@@ -120,8 +120,13 @@ int heat_readdat_bin(const char *fnam, int *nx, int *ny, float *u, size_t capaci
  * streams through the GPU in bands of rows (H2D of band i+1, all updates of band i -- time-skewed -- and
  * D2H of the rows that are final run at the same time; same bits as the plain loop).  Pass page-locked
  * memory (cudaHostAlloc / cudaHostRegister) to get that overlap; pageable memory works but copies
- * synchronously.  HEAT_SOLVE_STREAMED=0 switches the overlap off, HEAT_SOLVE_BAND_ROWS sets the band. */
+ * synchronously.  HEAT_SOLVE_STREAMED=0 switches the overlap off, HEAT_SOLVE_BAND_ROWS sets the band.
+ * The two device buffers of the call are kept for the next heat_solve of the same size on the same device (one
+ * pair at most; a call of another size frees it first) instead of paying cudaMalloc/cudaFree every time:
+ * heat_trim() releases them, HEAT_SOLVE_KEEP_BUFFERS=0 turns that off. */
 int heat_solve(const heat_params *p, float *grid, int *updates_done, int *converged);
+/* Frees what heat_solve keeps between calls (nothing else holds device memory after its handle is destroyed). */
+int heat_trim(void);
 /* The same for a double-precision grid (p->grid_type = HEAT_GRID_F64). */
 int heat_solve_f64(const heat_params *p, double *grid, int *updates_done, int *converged);
 

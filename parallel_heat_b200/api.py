@@ -62,6 +62,7 @@ SIGNATURES = {
     "heat_readdat_bin": (C.c_int, [C.c_char_p, _ip, _ip, _fp, C.c_size_t]),
     "heat_solve": (C.c_int, [C.POINTER(HeatParams), _fp, _ip, _ip]),
     "heat_solve_f64": (C.c_int, [C.POINTER(HeatParams), _dp, _ip, _ip]),
+    "heat_trim": (C.c_int, []),
     "heat_inidat_f64": (C.c_int, [C.c_int, C.c_int, _dp]),
     "heat_inidat3d": (C.c_int, [C.c_int, C.c_int, C.c_int, _fp]),
     "heat_upload_f64": (C.c_int, [_H, _dp]),
@@ -201,6 +202,11 @@ def solve(grid, steps, **params):
     else:
         _check(load().heat_solve(C.byref(p), g.ctypes.data_as(_fp), C.byref(done), C.byref(conv)))
     return g, done.value, bool(conv.value)
+
+
+def trim():
+    """heat_trim(): release the device buffers heat_solve keeps between calls."""
+    _check(load().heat_trim())
 
 
 def solve_gpus(grid, steps, ngpus, **params):

@@ -257,6 +257,7 @@ struct heat_handle {
     int tb_per_sm = 0;            // resident CTAs per SM of this handle's K4 instantiation (queried once)
     int sm_count = 148;
     bool loaded = false;          // a field has been uploaded / initialised (else the first use zero-fills)
+    bool keep_buffers = false;    // heat_solve's own handle: its two field buffers go to the one-entry cache when it is destroyed
     // neighbours: side 0 = north (lower rows), 1 = south, 2 = west (lower columns), 3 = east
     unsigned* d_edge_count = nullptr;    // [4] edge-CTA arrival counters of the fused strip ordering, per side
     unsigned long long* d_wait_prof = nullptr; // HEAT_PROFILE_WAIT=1: [8] ns waited / waits per side (heat_debug_wait_stats)
@@ -342,6 +343,66 @@ static int validate(const heat_params* p)
     return HEAT_OK;
 }
 
+// heat_solve() allocates and frees both field buffers on every call: 9 + 16 ms at 65536^2, 5 of 12 ms at 8192^2, for a call
+// whose useful part is bound by PCIe.  Its internal handle therefore hands the pair to a one-entry cache when it is
+// destroyed, and the next heat_solve of the same size on the same device takes it from there.  At most one pair is held
+// (a different size or device frees it first); heat_trim() releases it; HEAT_SOLVE_KEEP_BUFFERS=0 turns the cache off.
+// Handles made by heat_create() never use it.
+struct solve_buffer_cache {
+    std::mutex m;
+    int device = -1;
+    size_t bytes = 0;
+    float* buf[2] = {nullptr, nullptr};
+};
+static solve_buffer_cache g_solve_cache;
+
+static void cache_drop_locked()
+{
+    solve_buffer_cache& c = g_solve_cache;
+    if (!c.buf[0]) return;
+    int cur = -1;
+    cudaGetDevice(&cur);
+    if (cur != c.device) cudaSetDevice(c.device);
+    cudaFree(c.buf[0]);
+    cudaFree(c.buf[1]);
+    if (cur >= 0 && cur != c.device) cudaSetDevice(cur);
+    c.buf[0] = c.buf[1] = nullptr;
+    c.bytes = 0;
+    c.device = -1;
+    cudaGetLastError();
+}
+
+static bool cache_take(int device, size_t bytes, float** b0, float** b1)
+{
+    solve_buffer_cache& c = g_solve_cache;
+    std::lock_guard<std::mutex> guard(c.m);
+    if (!c.buf[0]) return false;
+    if (c.device != device || c.bytes != bytes) {
+        cache_drop_locked(); // make room: the caller is about to allocate another size
+        return false;
+    }
+    *b0 = c.buf[0], *b1 = c.buf[1];
+    c.buf[0] = c.buf[1] = nullptr;
+    c.bytes = 0;
+    c.device = -1;
+    return true;
+}
+
+static void cache_put(int device, size_t bytes, float* b0, float* b1)
+{
+    solve_buffer_cache& c = g_solve_cache;
+    std::lock_guard<std::mutex> guard(c.m);
+    cache_drop_locked();
+    c.device = device, c.bytes = bytes, c.buf[0] = b0, c.buf[1] = b1;
+}
+
+extern "C" int heat_trim(void)
+{
+    std::lock_guard<std::mutex> guard(g_solve_cache.m);
+    cache_drop_locked();
+    return HEAT_OK;
+}
+
 extern "C" int heat_destroy(heat_handle* h)
 {
     if (!h) return HEAT_OK;
@@ -350,8 +411,12 @@ extern "C" int heat_destroy(heat_handle* h)
     for (int s = 0; s < 4; s++)
         for (int k = 0; k < 3; k++)
             if (h->peer[s].ipc_base[k]) cudaIpcCloseMemHandle(h->peer[s].ipc_base[k]);
-    if (h->buf[0]) cudaFree(h->buf[0]);
-    if (h->buf[1]) cudaFree(h->buf[1]);
+    if (h->keep_buffers && h->buf[0] && h->buf[1]) {
+        cache_put(h->p.device, (size_t)h->nloc * h->pitch * sizeof(float), h->buf[0], h->buf[1]);
+    } else {
+        if (h->buf[0]) cudaFree(h->buf[0]);
+        if (h->buf[1]) cudaFree(h->buf[1]);
+    }
     if (h->flags) cudaFree(h->flags);
     if (h->d_resid) cudaFree(h->d_resid);
     if (h->d_edge_count) cudaFree(h->d_edge_count);
@@ -376,7 +441,10 @@ extern "C" int heat_destroy(heat_handle* h)
     return HEAT_OK;
 }
 
-extern "C" int heat_create(const heat_params* p_in, heat_handle** out)
+static int create_handle(const heat_params* p_in, heat_handle** out, bool solve_cache);
+extern "C" int heat_create(const heat_params* p_in, heat_handle** out) { return create_handle(p_in, out, false); }
+
+static int create_handle(const heat_params* p_in, heat_handle** out, bool solve_cache)
 {
     if (!out) return fail(HEAT_E_INVALID, "heat_create: null out");
     *out = nullptr;
@@ -425,8 +493,11 @@ extern "C" int heat_create(const heat_params* p_in, heat_handle** out)
             return c_;                                                                                 \
         }                                                                                              \
     } while (0)
-    CKH(cudaMalloc((void**)&h->buf[0], bytes));
-    CKH(cudaMalloc((void**)&h->buf[1], bytes));
+    h->keep_buffers = solve_cache && p->nranks == 1 && p->nranks_y == 1 && env_int("HEAT_SOLVE_KEEP_BUFFERS", 1) != 0;
+    if (!(h->keep_buffers && cache_take(p->device, bytes, &h->buf[0], &h->buf[1]))) {
+        CKH(cudaMalloc((void**)&h->buf[0], bytes));
+        CKH(cudaMalloc((void**)&h->buf[1], bytes));
+    }
     const size_t flag_bytes = GCOL_OFFSET + (p->nranks_y > 1 ? 4 * (size_t)h->nloc * sizeof(float) : 0);
     CKH(cudaMalloc((void**)&h->flags, flag_bytes));
     if (p->nranks_y > 1) h->gcol = (float*)((char*)h->flags + GCOL_OFFSET);
@@ -1570,7 +1641,7 @@ static int solve_host(const heat_params* p, void* grid, int es, int* updates_don
     };
     const double t0 = now();
     heat_handle* h = nullptr;
-    int rc = heat_create(p, &h);
+    int rc = create_handle(p, &h, true);
     if (rc) return rc;
     const double t1 = now();
     const long long total = (long long)p->steps + (p->step_convention == HEAT_STEPS_MPI ? 1 : 0);

@@ -672,3 +672,28 @@ def test_blocks_convergence_and_inidat(ph, oracle):
 def test_blocks_refuse_temporal_blocking(ph):
     with pytest.raises(ph.HeatError):
         ph.HeatSolver(64, 64, rank_y=0, nranks_y=2, temporal_block=2)
+
+
+def test_heat_solve_keeps_and_trims_its_buffers(ph, oracle, monkeypatch):
+    # heat_solve reuses the device buffers of its previous call of the same size (stale contents must not leak into the
+    # result: different fields, step counts, temporal blocking and grid types back to back), and heat_trim frees them
+    import torch
+    torch.cuda.synchronize()
+    ph.api.trim()
+    free0, _ = torch.cuda.mem_get_info()
+    a, b = field((700, 517), seed=1), field((700, 517), seed=2)
+    for u, steps, kw in [(a, 9, {}), (b, 3, {}), (a, 40, dict(temporal_block=4)), (b, 0, {}), (a, 7, dict(arith=2))]:
+        got, done, _ = ph.solve(u, steps, **kw)
+        assert done == steps
+        assert_same_bits(got, oracle.solve(u, steps, arith=kw.get("arith", 0))[0], f"kept buffers, steps={steps} {kw}")
+    held, _ = torch.cuda.mem_get_info()
+    assert free0 - held >= 2 * 700 * 517 * 4  # the pair is still there
+    got, _, _ = ph.solve(field((300, 200), seed=3), 5)  # another size replaces it
+    assert_same_bits(got, oracle.solve(field((300, 200), seed=3), 5, arith=0)[0])
+    ph.api.trim()
+    after, _ = torch.cuda.mem_get_info()
+    assert after >= free0 - (1 << 20)
+    monkeypatch.setenv("HEAT_SOLVE_KEEP_BUFFERS", "0")
+    ph.solve(a, 4)
+    nokeep, _ = torch.cuda.mem_get_info()
+    assert nokeep >= free0 - (1 << 20)
