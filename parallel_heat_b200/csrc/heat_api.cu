@@ -423,8 +423,7 @@ extern "C" int heat_destroy(heat_handle* h)
     if (h->d_wait_prof) cudaFree(h->d_wait_prof);
     if (h->res_halo) cudaFree(h->res_halo);
     if (h->res_flags) cudaFree(h->res_flags);
-    if (h->h_resid) cudaFreeHost(h->h_resid);
-    if (h->h_status) cudaFreeHost(h->h_status);
+    if (h->h_status) cudaFreeHost(h->h_status); // one pinned block: status word, then the residual words (h_resid)
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->ev_resid) cudaEventDestroy(h->ev_resid);
@@ -503,9 +502,10 @@ static int create_handle(const heat_params* p_in, heat_handle** out, bool solve_
     if (p->nranks_y > 1) h->gcol = (float*)((char*)h->flags + GCOL_OFFSET);
     CKH(cudaMalloc((void**)&h->d_resid, 2 * sizeof(unsigned)));
     CKH(cudaMalloc((void**)&h->d_edge_count, 4 * sizeof(unsigned)));
-    CKH(cudaHostAlloc((void**)&h->h_resid, 2 * sizeof(unsigned), cudaHostAllocDefault));
-    CKH(cudaHostAlloc((void**)&h->h_status, sizeof(int), cudaHostAllocMapped));
-    *h->h_status = 0;
+    // one pinned, mapped block for the host-visible words (a pinned allocation costs 0.5-1 ms): [0] time-out status, [2..3] residual
+    CKH(cudaHostAlloc((void**)&h->h_status, 4 * sizeof(unsigned), cudaHostAllocMapped));
+    memset(h->h_status, 0, 4 * sizeof(unsigned));
+    h->h_resid = (unsigned*)h->h_status + 2;
     CKH(cudaHostGetDevicePointer((void**)&h->d_status, h->h_status, 0));
     CKH(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     h->own_stream = true;
