@@ -125,10 +125,10 @@ int heat_readdat_bin(const char *fnam, int *nx, int *ny, float *u, size_t capaci
  * pair at most; a call of another size frees it first) instead of paying cudaMalloc/cudaFree every time:
  * heat_trim() releases them, HEAT_SOLVE_KEEP_BUFFERS=0 turns that off. */
 int heat_solve(const heat_params *p, float *grid, int *updates_done, int *converged);
-/* Frees what heat_solve keeps between calls (nothing else holds device memory after its handle is destroyed). */
-int heat_trim(void);
 /* The same for a double-precision grid (p->grid_type = HEAT_GRID_F64). */
 int heat_solve_f64(const heat_params *p, double *grid, int *updates_done, int *converged);
+/* Frees what heat_solve keeps between calls (nothing else holds device memory after its handle is destroyed). */
+int heat_trim(void);
 
 /* The same over the first `ngpus` devices of this process: one row strip per GPU, ghost rows moved by
  * peer stores over NVLink, one host thread.  Replaces M:51-297 (topology, scatter, halo requests, loop,
