@@ -146,3 +146,18 @@ def test_host_inidat_twins_match_the_oracle(ph, oracle):
     a, b = ph.inidat3d(33, 40, 52), oracle.inidat3d(33, 40, 52)
     assert a.shape == (33, 40, 52) and np.array_equal(a.view(np.uint32), b.view(np.uint32))
     assert (a[0] == 0).all() and (a[:, 0] == 0).all() and (a[:, :, -1] == 0).all()  # the ring starts at zero
+
+
+def test_parameter_combinations_are_refused_before_any_device_is_touched(ph):
+    # validate() runs first in heat_create, so these answers do not need a GPU
+    bad = [dict(nz=6), dict(nz=-1), dict(nz=8, temporal_block=2), dict(nz=8, rank_y=0, nranks_y=2),
+           dict(nz=8, grid_type=ph.GRID_F64), dict(grid_type=ph.GRID_F64, temporal_block=2),
+           dict(grid_type=ph.GRID_F64, rank_y=0, nranks_y=2), dict(grid_type=7), dict(temporal_block=5),
+           dict(rank=2, nranks=2), dict(arith=3), dict(conv_every=-1)]
+    for kw in bad:
+        with pytest.raises(ph.HeatError) as ei:
+            ph.HeatSolver(64, 64, **kw)
+        assert ei.value.code == ph.api.E_INVALID, kw
+    with pytest.raises(ph.HeatError) as ei:
+        ph.HeatSolver(64, 1000000, nz=4096)  # ny*nz must fit an int
+    assert ei.value.code == ph.api.E_INVALID and "fit an int" in str(ei.value)
