@@ -777,11 +777,14 @@ static cudaError_t launch_step_3d_t(heat_handle* h, const float* in, float* out,
     // every CTA of the first / last plane tile touches the neighbour on that side (same predicate as in the kernel)
     h->sync_args.count[0] = h->sync_args.count[1] = grid.x * grid.y;
     if (h->sync_args.counters)
-        heat_step_3d<ARITH, RESID, TY, WARPS, true><<<grid, 32 * WARPS, 0, h->stream>>>(
+        heat_step_3d<ARITH, RESID, TY, WARPS, true, true><<<grid, 32 * WARPS, 0, h->stream>>>(
+            in, out, h->upd_lo, h->upd_hi, ny, nz, h->pitch, ppt, h->p.cx, h->p.cy, h->p.cz, h->d_resid, peer_n, peer_s, h->sync_args);
+    else if (peer_n || peer_s)
+        heat_step_3d<ARITH, RESID, TY, WARPS, false, true><<<grid, 32 * WARPS, 0, h->stream>>>(
             in, out, h->upd_lo, h->upd_hi, ny, nz, h->pitch, ppt, h->p.cx, h->p.cy, h->p.cz, h->d_resid, peer_n, peer_s, h->sync_args);
     else
-        heat_step_3d<ARITH, RESID, TY, WARPS, false><<<grid, 32 * WARPS, 0, h->stream>>>(
-            in, out, h->upd_lo, h->upd_hi, ny, nz, h->pitch, ppt, h->p.cx, h->p.cy, h->p.cz, h->d_resid, peer_n, peer_s, h->sync_args);
+        heat_step_3d<ARITH, RESID, TY, WARPS, false, false><<<grid, 32 * WARPS, 0, h->stream>>>(
+            in, out, h->upd_lo, h->upd_hi, ny, nz, h->pitch, ppt, h->p.cx, h->p.cy, h->p.cz, h->d_resid, nullptr, nullptr, h->sync_args);
     h->launches++;
     return cudaGetLastError();
 }

@@ -1345,7 +1345,8 @@ __global__ void heat_inidat3d_kernel(float* __restrict__ a, float* __restrict__ 
 #define HEAT_3D_MINBLOCKS 4 // resident CTAs per SM asked of the compiler: 4 = 64 registers, no spills.  Measured at 640^3 /
 #endif                      // 1024^3: unconstrained (78 registers, 3 CTAs) 649 / 652 GLUP/s, 4: 716 / 709, 5 (48 registers, spills) 450 / 449
 
-template <int ARITH, bool RESID, int TY, int WARPS, bool SYNC>
+// PEERS = this strip has a neighbour to store ghost planes into (a single strip's instantiation carries none of that code)
+template <int ARITH, bool RESID, int TY, int WARPS, bool SYNC, bool PEERS>
 __global__ void __launch_bounds__(32 * WARPS, HEAT_3D_MINBLOCKS)
 heat_step_3d(const float* __restrict__ in, float* __restrict__ out, int plane_lo, int plane_hi, int ny, int nz, int64_t pitch,
              int planes_per_tile, float cx, float cy, float cz, unsigned* __restrict__ resid, float* peer_n, float* peer_s,
@@ -1403,8 +1404,8 @@ heat_step_3d(const float* __restrict__ in, float* __restrict__ out, int plane_lo
                     if (kw) o.w = cc.w;
                     if (live) {
                         st4(q + roff[k], o);
-                        if (peer_n && x == plane_lo) st4(peer_n + roff[k], o);
-                        if (peer_s && x == plane_hi - 1) st4(peer_s + roff[k], o);
+                        if (PEERS && peer_n && x == plane_lo) st4(peer_n + roff[k], o);
+                        if (PEERS && peer_s && x == plane_hi - 1) st4(peer_s + roff[k], o);
                     }
                     if (RESID) {
                         m = fmaxf(m, fabsf(__fsub_rn(cc.x, o.x)));
