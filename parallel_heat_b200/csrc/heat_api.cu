@@ -742,13 +742,17 @@ static cudaError_t launch_step_f64_t(heat_handle* h, const float* in, float* out
     count_edge_ctas(h, rows, rpt, grid.x, grid.y);
     const double cx = (double)h->p.cx, cy = (double)h->p.cy; // struct Parms stays float (M:29-32): the constants are 0.1f widened
     if (h->sync_args.counters)
-        heat_step_f64<FMA, RESID, true><<<grid, 128, 0, h->stream>>>((const double*)in, (double*)out, h->upd_lo, h->upd_hi, ny, epitch, rpt,
-                                                                    cx, cy, (unsigned long long*)h->d_resid, (double*)peer_n,
-                                                                    (double*)peer_s, h->ghost, reverse, h->sync_args);
-    else
-        heat_step_f64<FMA, RESID, false><<<grid, 128, 0, h->stream>>>((const double*)in, (double*)out, h->upd_lo, h->upd_hi, ny, epitch, rpt,
-                                                                     cx, cy, (unsigned long long*)h->d_resid, (double*)peer_n,
-                                                                     (double*)peer_s, h->ghost, reverse, h->sync_args);
+        heat_step_f64<FMA, RESID, true, true><<<grid, 128, 0, h->stream>>>((const double*)in, (double*)out, h->upd_lo, h->upd_hi, ny, epitch,
+                                                                          rpt, cx, cy, (unsigned long long*)h->d_resid, (double*)peer_n,
+                                                                          (double*)peer_s, h->ghost, reverse, h->sync_args);
+    else if (peer_n || peer_s)
+        heat_step_f64<FMA, RESID, false, true><<<grid, 128, 0, h->stream>>>((const double*)in, (double*)out, h->upd_lo, h->upd_hi, ny, epitch,
+                                                                           rpt, cx, cy, (unsigned long long*)h->d_resid, (double*)peer_n,
+                                                                           (double*)peer_s, h->ghost, reverse, h->sync_args);
+    else // a single strip's instantiation carries no peer-store code
+        heat_step_f64<FMA, RESID, false, false><<<grid, 128, 0, h->stream>>>((const double*)in, (double*)out, h->upd_lo, h->upd_hi, ny, epitch,
+                                                                            rpt, cx, cy, (unsigned long long*)h->d_resid, nullptr, nullptr,
+                                                                            h->ghost, reverse, h->sync_args);
     h->launches++;
     return cudaGetLastError();
 }

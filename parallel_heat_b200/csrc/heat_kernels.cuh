@@ -1192,7 +1192,7 @@ __device__ __forceinline__ void block_max_to_global64(double m, unsigned long lo
     }
 }
 
-template <bool FMA, bool RESID, bool SYNC>
+template <bool FMA, bool RESID, bool SYNC, bool PEERS>
 __global__ void __launch_bounds__(128, 8)
 heat_step_f64(const double* __restrict__ in, double* __restrict__ out, int row_lo, int row_hi, int ny, int64_t pitch,
               int rows_per_tile, double cx, double cy, unsigned long long* __restrict__ resid, double* peer_n, double* peer_s,
@@ -1246,9 +1246,9 @@ heat_step_f64(const double* __restrict__ in, double* __restrict__ out, int row_l
                     if (ky) o.y = c.y;
                     if (live) {
                         *reinterpret_cast<double2*>(q) = o;
-                        if (peer_n && r + u < row_lo + ghost)
+                        if (PEERS && peer_n && r + u < row_lo + ghost)
                             *reinterpret_cast<double2*>(peer_n + (int64_t)(r + u - row_lo) * pitch + col) = o;
-                        if (peer_s && r + u >= row_hi - ghost)
+                        if (PEERS && peer_s && r + u >= row_hi - ghost)
                             *reinterpret_cast<double2*>(peer_s + (int64_t)(r + u - (row_hi - ghost)) * pitch + col) = o;
                     }
                     if (RESID) {
