@@ -629,12 +629,16 @@ static cudaError_t launch_step_t(heat_handle* h, const float* in, float* out, fl
             dim3 g((unsigned)((h->pitch / 4 + THREADS - 1) / THREADS), (unsigned)((rows + ROWS - 1) / ROWS));
             count_edge_ctas(h, rows, ROWS, g.x, g.y);
             if (h->sync_args.counters)
-                heat_step_bulk<ARITH, RESID, ROWS, THREADS, true><<<g, THREADS, 0, h->stream>>>(
+                heat_step_bulk<ARITH, RESID, ROWS, THREADS, true, true><<<g, THREADS, 0, h->stream>>>(
                     in, out, h->upd_lo, h->upd_hi, ny, h->pitch, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse,
                     h->sync_args, h->d_status);
-            else
-                heat_step_bulk<ARITH, RESID, ROWS, THREADS, false><<<g, THREADS, 0, h->stream>>>(
+            else if (peer_n || peer_s)
+                heat_step_bulk<ARITH, RESID, ROWS, THREADS, false, true><<<g, THREADS, 0, h->stream>>>(
                     in, out, h->upd_lo, h->upd_hi, ny, h->pitch, h->p.cx, h->p.cy, h->d_resid, peer_n, peer_s, h->ghost, reverse,
+                    h->sync_args, h->d_status);
+            else // a single strip's instantiation carries no peer-store code
+                heat_step_bulk<ARITH, RESID, ROWS, THREADS, false, false><<<g, THREADS, 0, h->stream>>>(
+                    in, out, h->upd_lo, h->upd_hi, ny, h->pitch, h->p.cx, h->p.cy, h->d_resid, nullptr, nullptr, h->ghost, reverse,
                     h->sync_args, h->d_status);
             h->launches++;
             return cudaGetLastError();

@@ -699,7 +699,7 @@ heat_step_vec(const float* __restrict__ in, float* __restrict__ out, int row_lo,
 // 20-update repetitions): 8192^2 850 vs 852 GLUP/s for K1, 16384^2 862 vs 854, 65536^2 865 vs 851 -- it wins
 // where rows are long, so HEAT_K1_VARIANT=auto (the default) takes it for rows of 16384 floats and more.
 // Everything K1 does besides is here too: residual (K2), neighbour strips' ghost rows and step flags (K3).
-template <int ARITH, bool RESID, int ROWS, int THREADS, bool SYNC>
+template <int ARITH, bool RESID, int ROWS, int THREADS, bool SYNC, bool PEERS>
 __global__ void __launch_bounds__(THREADS)
 heat_step_bulk(const float* __restrict__ in, float* __restrict__ out, int row_lo, int row_hi, int ny, int64_t pitch, float cx,
                float cy, unsigned* __restrict__ resid, float* peer_n, float* peer_s, int ghost, int reverse, strip_sync sy,
@@ -765,8 +765,8 @@ heat_step_bulk(const float* __restrict__ in, float* __restrict__ out, int row_lo
             if (live) {
                 st4(q, o);
                 // K3: the first / last `ghost` updated rows are the neighbours' ghost rows
-                if (peer_n && r0 + i < row_lo + ghost) st4(peer_n + (int64_t)(r0 + i - row_lo) * pitch + col, o);
-                if (peer_s && r0 + i >= row_hi - ghost) st4(peer_s + (int64_t)(r0 + i - (row_hi - ghost)) * pitch + col, o);
+                if (PEERS && peer_n && r0 + i < row_lo + ghost) st4(peer_n + (int64_t)(r0 + i - row_lo) * pitch + col, o);
+                if (PEERS && peer_s && r0 + i >= row_hi - ghost) st4(peer_s + (int64_t)(r0 + i - (row_hi - ghost)) * pitch + col, o);
             }
             if (RESID) {
                 m = fmaxf(m, fabsf(__fsub_rn(c.x, o.x)));
