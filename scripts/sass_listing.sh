@@ -15,5 +15,5 @@ dump "heat_step_vecILi0ELb1ELi128ELi4ELb0ELb0" profiles/sass_heat_step_vec_fma_r
 dump "heat_step_tbILi0ELi4ELi1ELb0" profiles/sass_heat_step_tb_fma_T4.txt
 dump "heat_step_bulkILi0ELb0ELi8ELi128ELb0ELb0" profiles/sass_heat_step_bulk_fma.txt
 dump "heat_step_vecILi2ELb0ELi128ELi4ELb0ELb0" profiles/sass_heat_step_vec_f64mix.txt
-dump "heat_step_f64ILb1ELb0ELb0" profiles/sass_heat_step_f64_fma.txt
+dump "heat_step_f64ILb1ELb0ELb0ELb0" profiles/sass_heat_step_f64_fma.txt
 grep -cE "UTMALDG|UBLKCP|LDG.E.128|STG.E.128|SHFL|REDUX" profiles/sass_heat_step_vec_fma_residual.txt || true
